@@ -1,0 +1,850 @@
+// mmg_capi.cu — the C ABI of include/mola_b200/mmg.h: handle management and the host
+// side of every batched operation (staging, table/row growth, kernel sequencing).
+// All compute happens in the sm_100a kernels of mmg_voxel.cuh / mmg_trees.cuh; there
+// is deliberately no CPU path: without a CUDA device mmg_create fails.
+#include "../../include/mola_b200/mmg.h"
+#include "mmg_host.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+namespace mmg
+{
+unsigned long long        g_launches = 0;
+static thread_local char  g_err[512] = "";
+void set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+}  // namespace mmg
+using namespace mmg;
+
+// ------------------------------------------------------------------ helpers
+static PoseD make_pose(const double* pose12)
+{
+    PoseD              T;
+    static const double I[12] = {1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0};
+    memcpy(T.m, pose12 ? pose12 : I, sizeof(T.m));
+    return T;
+}
+
+void* mmg_map::scratch_get(int slot, size_t bytes)
+{
+    if (slot >= (int)scratch.size()) scratch.resize(slot + 1, {nullptr, 0});
+    auto& s = scratch[slot];
+    if (s.second < bytes)
+    {
+        if (s.first)
+        {
+            cudaDeviceSynchronize();
+            cudaFree(s.first);
+        }
+        const size_t want = bytes + bytes / 4 + 256;
+        if (cudaMalloc(&s.first, want) != cudaSuccess)
+        {
+            s = {nullptr, 0};
+            set_error("cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(cudaGetLastError()));
+            return nullptr;
+        }
+        s.second = want;
+    }
+    return s.first;
+}
+
+static int init_counters(mmg_map* m, bool keep_bbox)
+{
+    Counters c;
+    memset(&c, 0, sizeof(c));
+    if (keep_bbox)
+    {
+        Counters old;
+        MMG_CUDA(cudaMemcpy(&old, m->dev.ctr, sizeof(old), cudaMemcpyDeviceToHost));
+        memcpy(c.bbox, old.bbox, sizeof(c.bbox));
+    }
+    else
+    {
+        c.bbox[0] = c.bbox[1] = c.bbox[2] = 0xFFFFFFFFu;
+        c.bbox[3] = c.bbox[4] = c.bbox[5] = 0u;
+    }
+    MMG_CUDA(cudaMemcpy(m->dev.ctr, &c, sizeof(c), cudaMemcpyHostToDevice));
+    m->h_nvox_hi = 0;
+    m->h_free_n  = 0;
+    return MMG_OK;
+}
+
+static int alloc_table(mmg_map* m, u64 cap)
+{
+    Entry* t = nullptr;
+    if (cudaMalloc(&t, cap * sizeof(Entry)) != cudaSuccess)
+    {
+        set_error("cudaMalloc table (%llu entries) failed", (unsigned long long)cap);
+        cudaGetLastError();
+        return MMG_ERR_OUT_OF_MEM;
+    }
+    MMG_CUDA(cudaMemset(t, 0xFF, cap * sizeof(Entry)));
+    if (m->dev.table) cudaFree(m->dev.table);
+    m->dev.table = t;
+    m->dev.mask  = cap - 1;
+    m->cap       = cap;
+    return MMG_OK;
+}
+
+// Makes room for `entries` keys at load factor <= 0.5 (the reference's robin_map also keeps
+// max load 0.5); rebuilds the table from the live rows when it grows.
+static int ensure_table(mmg_map* m, u64 entries, cudaStream_t st)
+{
+    u64 cap = 1024;
+    while (cap < 2 * entries) cap <<= 1;
+    if (cap <= m->cap) return MMG_OK;
+    MMG_CUDA(cudaStreamSynchronize(st));
+    int rc = alloc_table(m, cap);
+    if (rc) return rc;
+    if (m->h_nvox_hi) MMG_LAUNCH(k_rebuild_table, (m->h_nvox_hi + 255) / 256, 256, 0, st, m->dev, m->h_nvox_hi);
+    return MMG_OK;
+}
+
+template <typename T>
+static int grow_array(T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
+{
+    T* q = nullptr;
+    if (cudaMalloc(&q, newn * sizeof(T)) != cudaSuccess)
+    {
+        set_error("cudaMalloc(%llu B) failed", (unsigned long long)(newn * sizeof(T)));
+        cudaGetLastError();
+        return MMG_ERR_OUT_OF_MEM;
+    }
+    if (oldn) MMG_CUDA(cudaMemcpyAsync(q, *p, oldn * sizeof(T), cudaMemcpyDeviceToDevice, st));
+    MMG_CUDA(cudaMemsetAsync(q + oldn, fill_byte, (newn - oldn) * sizeof(T), st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    if (*p) cudaFree(*p);
+    *p = q;
+    return MMG_OK;
+}
+
+static int ensure_rows(mmg_map* m, u64 rows, cudaStream_t st)
+{
+    if (rows <= m->rowcap) return MMG_OK;
+    const u64 newcap = std::max<u64>(rows + rows / 2, 4096);
+    const u64 cap_pts = (u64)m->row_points();
+    int       rc;
+    if ((rc = grow_array(&m->dev.pts, m->rowcap * cap_pts, newcap * cap_pts, 0, st))) return rc;
+    if ((rc = grow_array(&m->dev.cnt, m->rowcap, newcap, 0, st))) return rc;
+    if ((rc = grow_array(&m->dev.vkey, m->rowcap, newcap, 0xFF, st))) return rc;
+    if ((rc = grow_array(&m->dev.free_list, m->rowcap, newcap, 0, st))) return rc;
+    if (m->kind == MMG_SPARSE_VOXEL && (rc = grow_array(&m->dev.mean, m->rowcap, newcap, 0, st))) return rc;
+    m->rowcap = newcap;
+    return MMG_OK;
+}
+
+static int read_counters(mmg_map* m, Counters* c, cudaStream_t st)
+{
+    MMG_CUDA(cudaMemcpyAsync(m->h_ctr, m->dev.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    *c = *m->h_ctr;
+    return MMG_OK;
+}
+
+// Stages caller SoA inputs on the device when they live in host memory.
+static int stage_in(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, int mem, cudaStream_t st, const float** dx,
+                    const float** dy, const float** dz)
+{
+    if (mem == MMG_MEM_DEVICE)
+    {
+        *dx = xs, *dy = ys, *dz = zs;
+        return MMG_OK;
+    }
+    float* b = (float*)m->scratch_get(S_IN, 3 * n * sizeof(float));
+    if (!b) return MMG_ERR_OUT_OF_MEM;
+    MMG_CUDA(cudaMemcpyAsync(b, xs, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    MMG_CUDA(cudaMemcpyAsync(b + n, ys, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    MMG_CUDA(cudaMemcpyAsync(b + 2 * n, zs, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    *dx = b, *dy = b + n, *dz = b + 2 * n;
+    return MMG_OK;
+}
+
+static unsigned persistent_blocks(const mmg_map* m, size_t work_warps, int warps_per_block, int blocks_per_sm)
+{
+    const size_t need = (work_warps + warps_per_block - 1) / warps_per_block;
+    return (unsigned)std::max<size_t>(1, std::min<size_t>(need, (size_t)m->num_sms * blocks_per_sm));
+}
+
+// ------------------------------------------------------------------ insert
+template <class Tr>
+static int insert_voxel(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, int has_robot_pose, int mem,
+                        cudaStream_t st)
+{
+    const mmg_params& P = m->prm;
+    // far-voxel eviction, HashedVoxelPointCloud.cpp:305-326 (Hashed only)
+    if (m->kind == MMG_HASHED_VOXEL && has_robot_pose && pose12 && P.remove_voxels_farther_than > 0 && m->h_nvox_hi > 0)
+    {
+        const int   dist_in_grid = (int)std::ceil(P.remove_voxels_farther_than * (double)m->inv);
+        const float t[3]         = {(float)pose12[9], (float)pose12[10], (float)pose12[11]};
+        const int   ox = (int)(t[0] * m->inv), oy = (int)(t[1] * m->inv), oz = (int)(t[2] * m->inv);
+        MMG_LAUNCH(k_evict, (m->h_nvox_hi + 255) / 256, 256, 0, st, m->dev, m->h_nvox_hi, ox, oy, oz, dist_in_grid);
+        Counters c;
+        int      rc = read_counters(m, &c, st);
+        if (rc) return rc;
+        if (c.free_n != m->h_free_n)
+        {  // something was evicted: rebuild the (tombstone-free) table from the live rows
+            m->h_free_n = c.free_n;
+            MMG_CUDA(cudaMemsetAsync(m->dev.table, 0xFF, m->cap * sizeof(Entry), st));
+            MMG_LAUNCH(k_rebuild_table, (m->h_nvox_hi + 255) / 256, 256, 0, st, m->dev, m->h_nvox_hi);
+        }
+    }
+    if (n == 0) return MMG_OK;
+    if (n >= (1ull << 31))
+    {
+        set_error("insert batch too large (%zu points; limit 2^31-1)", n);
+        return MMG_ERR_INVALID_ARG;
+    }
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    const u64 live = m->h_nvox_hi - m->h_free_n;
+    if ((rc = ensure_table(m, live + n, st))) return rc;
+
+    const u32 nb    = (u32)sort_nblocks(n);
+    float4*   gp    = (float4*)m->scratch_get(S_GP, n * sizeof(float4));
+    u32*      vid   = (u32*)m->scratch_get(S_VID, n * sizeof(u32));
+    u32*      sbuf  = (u32*)m->scratch_get(S_SORT, (3 * n + (size_t)RS_RADIX * nb + scan_scratch_elems((size_t)RS_RADIX * nb)) * sizeof(u32));
+    u32*      segs  = (u32*)m->scratch_get(S_SEG, n * sizeof(u32));
+    if (!gp || !vid || !sbuf || !segs) return MMG_ERR_OUT_OF_MEM;
+    SortScratch ss{sbuf, sbuf + n, sbuf + 2 * n, sbuf + 3 * n, sbuf + 3 * n + (size_t)RS_RADIX * nb};
+
+    const u32   hard      = (u32)Tr::CAP;
+    const bool  min_dist  = (m->kind == MMG_HASHED_VOXEL) && P.min_distance_between_points > 0.f;
+    const float thr       = min_dist ? P.min_distance_between_points * P.min_distance_between_points : 0.f;
+    const bool  use_thr   = min_dist && thr > 0.f;
+    const bool  uncapped  = (P.max_points_per_voxel == 0 || P.max_points_per_voxel > hard);
+    const int   bbox_all  = (!use_thr && uncapped) ? 1 : 0;
+    const int   bbox_acc  = (!use_thr && !uncapped) ? 1 : 0;
+
+    MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->nseg, 0, sizeof(u32), st));
+    MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->oob, 0, sizeof(u32), st));
+    const PoseD T = make_pose(pose12);
+    MMG_LAUNCH((k_locate<Tr>), (unsigned)((n + 255) / 256), 256, 0, st, dx, dy, dz, (u32)n, T, m->inv, m->dev, gp, vid, bbox_all);
+    Counters c;
+    if ((rc = read_counters(m, &c, st))) return rc;
+    m->h_nvox_hi = c.nvox_hi;
+    m->h_free_n  = c.free_n;
+    if ((rc = ensure_rows(m, c.nvox_hi, st))) return rc;
+
+    u32 *svid, *sidx;
+    radix_sort_index(vid, n, c.nvox_hi, ss, &svid, &sidx, st);
+    MMG_LAUNCH(k_segment_heads, (unsigned)((n + 255) / 256), 256, 0, st, svid, (u32)n, c.nvox_hi, segs, m->dev.ctr);
+    const unsigned fb = persistent_blocks(m, n, 8, 8);
+    MMG_LAUNCH((k_fold<Tr>), fb, 256, 0, st, m->dev, svid, sidx, segs, (u32)n, gp, m->inv, P.max_points_per_voxel, use_thr ? thr : 0.f, bbox_acc,
+               m->kind == MMG_SPARSE_VOXEL ? 1 : 0);
+    MMG_CUDA(cudaGetLastError());
+    if (mem == MMG_MEM_HOST) MMG_CUDA(cudaStreamSynchronize(st));
+    m->points_dirty = true;
+    if (c.oob)
+    {
+        set_error("%u of %zu points have a voxel index outside +-2^20 and were skipped", c.oob, n);
+        return MMG_ERR_OUT_OF_RANGE;
+    }
+    return MMG_OK;
+}
+
+// ------------------------------------------------------------------ queries
+struct OutBufs
+{
+    uint8_t* found;
+    float *  xyz, *d2;
+    u64*     id;
+    u32*     count;
+};
+
+template <class Tr>
+static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, size_t stride, const double* pose12,
+                           uint8_t* ofound, float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st)
+{
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (n == 0) return MMG_OK;
+    const size_t nq = (n + stride - 1) / stride;
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    QueryOut o{ofound, oxyz, od2, (u64*)oid};
+    char*    ob = nullptr;
+    if (mem == MMG_MEM_HOST)
+    {
+        ob = (char*)m->scratch_get(S_OUT, nq * 32);
+        if (!ob) return MMG_ERR_OUT_OF_MEM;
+        o.id = (u64*)ob, o.xyz = (float*)(ob + nq * 8), o.d2 = (float*)(ob + nq * 20), o.found = (uint8_t*)(ob + nq * 24);
+    }
+    const PoseD    T  = make_pose(pose12);
+    const unsigned nb = persistent_blocks(m, nq, 8, 8);
+    MMG_LAUNCH((k_nn_single<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, o);
+    MMG_CUDA(cudaGetLastError());
+    if (mem == MMG_MEM_HOST)
+    {
+        MMG_CUDA(cudaMemcpyAsync(oid, o.id, nq * 8, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(oxyz, o.xyz, nq * 12, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(od2, o.d2, nq * 4, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(ofound, o.found, nq, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaStreamSynchronize(st));
+    }
+    return MMG_OK;
+}
+
+template <class Tr, int K, bool REF>
+static int nn_multi_voxel(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, size_t k,
+                          uint32_t* ocount, float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st)
+{
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (n == 0) return MMG_OK;
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    u32*   dc = ocount;
+    float *dxyz = oxyz, *dd2 = od2;
+    u64*   did = (u64*)oid;
+    if (mem == MMG_MEM_HOST)
+    {
+        char* ob = (char*)m->scratch_get(S_OUT, n * k * 24 + n * 4 + 64);
+        if (!ob) return MMG_ERR_OUT_OF_MEM;
+        did = (u64*)ob, dxyz = (float*)(ob + n * k * 8), dd2 = (float*)(ob + n * k * 20), dc = (u32*)(ob + n * k * 24);
+    }
+    const PoseD T = make_pose(pose12);
+    MMG_LAUNCH((k_nn_multi<Tr, K, REF>), (unsigned)((n + 127) / 128), 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, (u32)k, dc, dxyz,
+               dd2, did);
+    MMG_CUDA(cudaGetLastError());
+    if (mem == MMG_MEM_HOST)
+    {
+        MMG_CUDA(cudaMemcpyAsync(oid, did, n * k * 8, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(oxyz, dxyz, n * k * 12, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(od2, dd2, n * k * 4, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(ocount, dc, n * 4, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaStreamSynchronize(st));
+    }
+    return MMG_OK;
+}
+
+template <class Tr>
+static int radius_hashed(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float r2, size_t maxp,
+                         uint64_t* ooff, uint64_t* ototal, int mem, cudaStream_t st)
+{
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    u32* counts = (u32*)m->scratch_get(S_RCNT, (n + 1) * sizeof(u32));
+    u64* offs   = (u64*)m->scratch_get(S_ROFF, (n + 1 + scan_scratch_elems(n)) * sizeof(u64));
+    if (!counts || !offs) return MMG_ERR_OUT_OF_MEM;
+    const PoseD T = make_pose(pose12);
+    const float r = r2 > 0 ? std::sqrt(r2) : 0.f;
+    const u32   mp = (u32)std::min<size_t>(maxp, 0xFFFFFFFFu);
+    const unsigned g = (unsigned)((n + 127) / 128);
+    MMG_LAUNCH((k_radius_hashed<Tr, 0>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, r2, r, mp, counts, (const u64*)nullptr,
+               (float*)nullptr, (float*)nullptr, (u64*)nullptr);
+    exclusive_scan<u32, u64>(counts, offs, n, offs + n, offs + n + 1, st);
+    u64 total = 0;
+    MMG_CUDA(cudaMemcpyAsync(&total, offs + n, sizeof(u64), cudaMemcpyDeviceToHost, st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    m->rad_total = total;
+    char* hb     = (char*)m->scratch_get(S_RHITS, std::max<u64>(total, 1) * 24);
+    if (!hb) return MMG_ERR_OUT_OF_MEM;
+    m->rad_id = (u64*)hb, m->rad_xyz = (float*)(hb + total * 8), m->rad_d2 = (float*)(hb + total * 20);
+    if (total)
+        MMG_LAUNCH((k_radius_hashed<Tr, 1>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, r2, r, mp, counts, offs, m->rad_xyz,
+                   m->rad_d2, m->rad_id);
+    MMG_CUDA(cudaGetLastError());
+    if (mem == MMG_MEM_HOST)
+        MMG_CUDA(cudaMemcpyAsync(ooff, offs, (n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    else
+        MMG_CUDA(cudaMemcpyAsync(ooff, offs, (n + 1) * sizeof(u64), cudaMemcpyDeviceToDevice, st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    if (ototal) *ototal = total;
+    return MMG_OK;
+}
+
+// ------------------------------------------------------------------ C ABI
+#define MMG_CHECK_MAP(m)                          \
+    if (!(m))                                     \
+    {                                             \
+        set_error("null map handle");             \
+        return MMG_ERR_INVALID_ARG;               \
+    }                                             \
+    MMG_CUDA(cudaSetDevice((m)->device))
+
+extern "C" {
+
+int mmg_default_params(int kind, mmg_params* p)
+{
+    if (!p || kind < 0 || kind > 2) return MMG_ERR_INVALID_ARG;
+    memset(p, 0, sizeof(*p));
+    // HashedVoxelPointCloud.h:119 (1.0), SparseVoxelPointCloud.h:158 (0.20), SparseTreesPointCloud.h:113 (10.0)
+    p->voxel_size                  = kind == MMG_HASHED_VOXEL ? 1.0f : (kind == MMG_SPARSE_VOXEL ? 0.20f : 10.0f);
+    p->max_points_per_voxel        = 0;
+    p->remove_voxels_farther_than  = 0.0;
+    p->min_distance_between_points = 0.f;
+    p->minimum_points_clearance    = 0.20f;  // SparseTreesPointCloud.h:337
+    p->sigma_dist                  = 0.5;
+    p->max_corr_distance           = 1.0;
+    p->decimation                  = 10;
+    p->match_mean                  = 0;
+    return MMG_OK;
+}
+
+int mmg_create(int kind, const mmg_params* p, int device, mmg_map** out)
+{
+    if (!p || !out || kind < 0 || kind > 2 || !(p->voxel_size > 0.f))
+    {
+        set_error("mmg_create: invalid argument");
+        return MMG_ERR_INVALID_ARG;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    {
+        cudaGetLastError();
+        set_error("no CUDA device: this library has no CPU path");
+        return MMG_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= ndev)
+    {
+        set_error("device %d out of range (%d devices)", device, ndev);
+        return MMG_ERR_INVALID_ARG;
+    }
+    MMG_CUDA(cudaSetDevice(device));
+    mmg_map* m = new mmg_map();
+    m->kind    = kind;
+    m->device  = device;
+    m->prm     = *p;
+    m->inv     = 1.0f / p->voxel_size;
+    MMG_CUDA(cudaDeviceGetAttribute(&m->num_sms, cudaDevAttrMultiProcessorCount, device));
+    MMG_CUDA(cudaMalloc(&m->dev.ctr, sizeof(Counters)));
+    MMG_CUDA(cudaMallocHost(&m->h_ctr, sizeof(Counters)));
+    int rc = init_counters(m, false);
+    if (!rc && kind != MMG_SPARSE_TREES) rc = alloc_table(m, 1u << 16);
+    if (!rc && kind == MMG_SPARSE_TREES) rc = trees_create(m);
+    if (rc)
+    {
+        mmg_destroy(m);
+        return rc;
+    }
+    *out = m;
+    return MMG_OK;
+}
+
+int mmg_destroy(mmg_map* m)
+{
+    if (!m) return MMG_OK;
+    cudaSetDevice(m->device);
+    cudaDeviceSynchronize();
+    if (m->kind == MMG_SPARSE_TREES) trees_destroy(m);
+    cudaFree(m->dev.table), cudaFree(m->dev.pts), cudaFree(m->dev.cnt), cudaFree(m->dev.vkey), cudaFree(m->dev.mean), cudaFree(m->dev.free_list),
+        cudaFree(m->dev.ctr);
+    if (m->h_ctr) cudaFreeHost(m->h_ctr);
+    for (auto& s : m->scratch)
+        if (s.first) cudaFree(s.first);
+    delete m;
+    return MMG_OK;
+}
+
+int mmg_clear(mmg_map* m)
+{
+    MMG_CHECK_MAP(m);
+    MMG_CUDA(cudaDeviceSynchronize());
+    if (m->kind == MMG_SPARSE_TREES) return trees_clear(m);
+    // internal_clear() drops the voxels but leaves the cached bounding box (HashedVoxelPointCloud.cpp:287)
+    MMG_CUDA(cudaMemset(m->dev.table, 0xFF, m->cap * sizeof(Entry)));
+    if (m->rowcap)
+    {
+        MMG_CUDA(cudaMemset(m->dev.cnt, 0, m->rowcap * sizeof(u32)));
+        MMG_CUDA(cudaMemset(m->dev.vkey, 0xFF, m->rowcap * sizeof(u64)));
+    }
+    return init_counters(m, true);
+}
+
+int mmg_set_params(mmg_map* m, const mmg_params* p)
+{
+    MMG_CHECK_MAP(m);
+    if (!p || !(p->voxel_size > 0.f)) return MMG_ERR_INVALID_ARG;
+    const bool resize = p->voxel_size != m->prm.voxel_size;
+    m->prm            = *p;
+    if (resize)
+    {  // setVoxelProperties(): recompute derived fields and clear, HashedVoxelPointCloud.cpp:189-200
+        m->inv = 1.0f / p->voxel_size;
+        if (m->kind == MMG_SPARSE_TREES) trees_set_grid(m);
+        return mmg_clear(m);
+    }
+    return MMG_OK;
+}
+int mmg_get_params(const mmg_map* m, mmg_params* p)
+{
+    if (!m || !p) return MMG_ERR_INVALID_ARG;
+    *p = m->prm;
+    return MMG_OK;
+}
+
+int mmg_insert_batch(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, int has_robot_pose, int mem,
+                     void* stream)
+{
+    MMG_CHECK_MAP(m);
+    if (n && (!xs || !ys || !zs)) return MMG_ERR_INVALID_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (m->kind)
+    {
+        case MMG_HASHED_VOXEL: return insert_voxel<HashedTraits>(m, xs, ys, zs, n, pose12, has_robot_pose, mem, st);
+        case MMG_SPARSE_VOXEL: return insert_voxel<SparseVoxelTraits>(m, xs, ys, zs, n, pose12, has_robot_pose, mem, st);
+        default: return trees_insert(m, xs, ys, zs, n, pose12, has_robot_pose, mem, st);
+    }
+}
+
+int mmg_nn_single_batch(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, uint8_t* out_found,
+                        float* out_xyz, float* out_d2, uint64_t* out_id, int mem, void* stream)
+{
+    MMG_CHECK_MAP(m);
+    if (n && (!xs || !ys || !zs || !out_found || !out_xyz || !out_d2 || !out_id)) return MMG_ERR_INVALID_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (m->kind)
+    {
+        case MMG_HASHED_VOXEL: return nn_single_voxel<HashedTraits>(m, xs, ys, zs, n, 1, pose12, out_found, out_xyz, out_d2, out_id, mem, st);
+        case MMG_SPARSE_VOXEL:
+            // extension: the reference throws here (SparseVoxelPointCloud.cpp:695-719);
+            // the host class keeps that behaviour unless the k-NN extension is enabled.
+            return nn_single_voxel<SparseVoxelTraits>(m, xs, ys, zs, n, 1, pose12, out_found, out_xyz, out_d2, out_id, mem, st);
+        default: return trees_nn_single(m, xs, ys, zs, n, 1, pose12, out_found, out_xyz, out_d2, out_id, mem, st);
+    }
+}
+
+int mmg_nn_multi_batch(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, size_t k,
+                       uint32_t* out_count, float* out_xyz, float* out_d2, uint64_t* out_id, int mem, void* stream)
+{
+    MMG_CHECK_MAP(m);
+    if (k == 0)
+    {  // ASSERT_(N > 0), HashedVoxelPointCloud.cpp:702
+        set_error("nn_multiple_search: N must be > 0");
+        return MMG_ERR_INVALID_ARG;
+    }
+    if (n && (!xs || !ys || !zs || !out_count || !out_xyz || !out_d2 || !out_id)) return MMG_ERR_INVALID_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (m->kind)
+    {
+        case MMG_HASHED_VOXEL: return nn_multi_voxel<HashedTraits, 3, true>(m, xs, ys, zs, n, pose12, k, out_count, out_xyz, out_d2, out_id, mem, st);
+        case MMG_SPARSE_VOXEL:
+            if (k > 8)
+            {
+                set_error("SparseVoxel k-NN extension supports k <= 8");
+                return MMG_ERR_UNSUPPORTED;
+            }
+            return nn_multi_voxel<SparseVoxelTraits, 8, false>(m, xs, ys, zs, n, pose12, k, out_count, out_xyz, out_d2, out_id, mem, st);
+        default: return trees_nn_multi(m, xs, ys, zs, n, pose12, k, out_count, out_xyz, out_d2, out_id, mem, st);
+    }
+}
+
+int mmg_nn_radius_batch(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float radius_sqr,
+                        size_t max_points, uint64_t* out_offsets, uint64_t* out_total, int mem, void* stream)
+{
+    MMG_CHECK_MAP(m);
+    if (!out_offsets || (n && (!xs || !ys || !zs))) return MMG_ERR_INVALID_ARG;
+    if (n >= (1ull << 31)) return MMG_ERR_INVALID_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (m->kind)
+    {
+        case MMG_HASHED_VOXEL: return radius_hashed<HashedTraits>(m, xs, ys, zs, n, pose12, radius_sqr, max_points, out_offsets, out_total, mem, st);
+        case MMG_SPARSE_VOXEL: return sv_radius(m, xs, ys, zs, n, pose12, radius_sqr, max_points, out_offsets, out_total, mem, st);
+        default: return trees_radius(m, xs, ys, zs, n, pose12, radius_sqr, max_points, out_offsets, out_total, mem, st);
+    }
+}
+
+int mmg_nn_radius_fetch(mmg_map* m, float* out_xyz, float* out_d2, uint64_t* out_id, int mem, void* stream)
+{
+    MMG_CHECK_MAP(m);
+    cudaStream_t st = (cudaStream_t)stream;
+    const u64    t  = m->rad_total;
+    if (!t) return MMG_OK;
+    const cudaMemcpyKind k = mem == MMG_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+    MMG_CUDA(cudaMemcpyAsync(out_xyz, m->rad_xyz, t * 12, k, st));
+    MMG_CUDA(cudaMemcpyAsync(out_d2, m->rad_d2, t * 4, k, st));
+    MMG_CUDA(cudaMemcpyAsync(out_id, m->rad_id, t * 8, k, st));
+    if (mem == MMG_MEM_HOST) MMG_CUDA(cudaStreamSynchronize(st));
+    return MMG_OK;
+}
+
+int mmg_likelihood(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, double* out_loglik, int mem,
+                   void* stream)
+{
+    MMG_CHECK_MAP(cm);
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (!out_loglik) return MMG_ERR_INVALID_ARG;
+    int empty = 0;
+    mmg_is_empty(m, &empty);
+    if (empty || n == 0)
+    {  // isEmpty() -> 0, HashedVoxelPointCloud.cpp:445; no points -> 0, :460
+        *out_loglik = 0.0;
+        return MMG_OK;
+    }
+    if (!(m->prm.sigma_dist > 0) || m->prm.decimation == 0)
+    {  // ASSERT_GT_(sigma_dist, 0) :515
+        set_error("likelihood: sigma_dist must be > 0 and decimation >= 1");
+        return MMG_ERR_INVALID_ARG;
+    }
+    if (m->kind == MMG_SPARSE_VOXEL)
+    {  // calls nn_single_search, which throws for this map type (SparseVoxelPointCloud.cpp:695-719)
+        set_error("n-search not available in this map type");
+        return MMG_ERR_UNSUPPORTED;
+    }
+    cudaStream_t st     = (cudaStream_t)stream;
+    const size_t stride = m->prm.decimation;
+    const size_t nq     = (n + stride - 1) / stride;
+    // results stay on the device: stage the input ourselves, then call the device path
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    char* ob = (char*)m->scratch_get(S_LIK, nq * 32 + 64);
+    if (!ob) return MMG_ERR_OUT_OF_MEM;
+    uint64_t* id  = (uint64_t*)ob;
+    float*   xyz = (float*)(ob + nq * 8);
+    float*   d2  = (float*)(ob + nq * 20);
+    uint8_t* fnd = (uint8_t*)(ob + nq * 24);
+    double*  sum = (double*)(ob + ((nq * 25 + 63) / 8) * 8);
+    if (m->kind == MMG_HASHED_VOXEL)
+        rc = nn_single_voxel<HashedTraits>(m, dx, dy, dz, n, stride, pose12, fnd, xyz, d2, id, MMG_MEM_DEVICE, st);
+    else
+        rc = trees_nn_single(m, dx, dy, dz, n, stride, pose12, fnd, xyz, d2, id, MMG_MEM_DEVICE, st);
+    if (rc) return rc;
+    const float max_sqr = (float)(m->prm.max_corr_distance * m->prm.max_corr_distance);
+    MMG_LAUNCH(k_likelihood_sum, 1, 1024, 0, st, fnd, d2, (u32)nq, max_sqr, sum);
+    double h = 0;
+    MMG_CUDA(cudaMemcpyAsync(&h, sum, sizeof(double), cudaMemcpyDeviceToHost, st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    *out_loglik = -(h / (double)nq) / m->prm.sigma_dist;
+    return MMG_OK;
+}
+
+int mmg_is_empty(const mmg_map* m, int* out_empty)
+{
+    if (!m || !out_empty) return MMG_ERR_INVALID_ARG;
+    if (m->kind == MMG_SPARSE_TREES) return trees_is_empty(m, out_empty);
+    *out_empty = (m->h_nvox_hi - m->h_free_n) == 0;
+    return MMG_OK;
+}
+
+int mmg_bbox(mmg_map* m, float out[6])
+{
+    MMG_CHECK_MAP(m);
+    if (!out) return MMG_ERR_INVALID_ARG;
+    Counters c;
+    int      rc = read_counters(m, &c, 0);
+    if (rc) return rc;
+    if (c.bbox[0] == 0xFFFFFFFFu && c.bbox[3] == 0u)
+    {  // not cached yet: boundingBox() computes it from the voxels / blocks / points and caches it
+        int empty = 0;
+        mmg_is_empty(m, &empty);
+        if (empty)
+        {
+            const u32 z = float_to_ordered(0.0f);
+            for (int i = 0; i < 6; i++) c.bbox[i] = z;
+            MMG_CUDA(cudaMemcpy(m->dev.ctr->bbox, c.bbox, sizeof(c.bbox), cudaMemcpyHostToDevice));
+        }
+        else
+        {
+            if (m->kind == MMG_HASHED_VOXEL)
+                MMG_LAUNCH((k_bbox_from_voxels<HashedTraits>), (m->h_nvox_hi + 255) / 256, 256, 0, 0, m->dev, m->h_nvox_hi, m->prm.voxel_size,
+                           m->dev.ctr->bbox);
+            else if (m->kind == MMG_SPARSE_VOXEL)
+                MMG_LAUNCH((k_bbox_from_voxels<SparseVoxelTraits>), (m->h_nvox_hi + 255) / 256, 256, 0, 0, m->dev, m->h_nvox_hi, m->prm.voxel_size,
+                           m->dev.ctr->bbox);
+            else if ((rc = trees_bbox_from_points(m)))
+                return rc;
+            if ((rc = read_counters(m, &c, 0))) return rc;
+        }
+    }
+    for (int i = 0; i < 6; i++) out[i] = ordered_to_float(c.bbox[i]);
+    return MMG_OK;
+}
+
+int mmg_num_voxels(const mmg_map* m, uint64_t* out_v)
+{
+    if (!m || !out_v) return MMG_ERR_INVALID_ARG;
+    if (m->kind == MMG_SPARSE_TREES) return trees_num_blocks(m, out_v);
+    *out_v = m->h_nvox_hi - m->h_free_n;
+    return MMG_OK;
+}
+
+int mmg_row_capacity(const mmg_map* m, uint32_t* out_cap)
+{
+    if (!m || !out_cap) return MMG_ERR_INVALID_ARG;
+    if (m->kind == MMG_SPARSE_TREES) return trees_row_capacity(m, out_cap);
+    *out_cap = (uint32_t)m->row_points();
+    return MMG_OK;
+}
+
+static int export_voxel(const mmg_map* cm, int32_t* keys, uint32_t* counts, float* points, float* means, float* cov, int mem, cudaStream_t st)
+{
+    mmg_map*  m  = const_cast<mmg_map*>(cm);
+    const u32 nr = m->h_nvox_hi;
+    const u64 V  = m->h_nvox_hi - m->h_free_n;
+    if (!V) return MMG_OK;
+    const u32 cap = (u32)m->row_points();
+    u32*      lr  = (u32*)m->scratch_get(S_SEG, (2 * (size_t)nr + 2 + scan_scratch_elems(nr)) * sizeof(u32));
+    if (!lr) return MMG_ERR_OUT_OF_MEM;
+    u32* rank = lr + nr + 1;
+    MMG_LAUNCH(k_live_flags, (nr + 255) / 256, 256, 0, st, m->dev, nr, lr);
+    exclusive_scan<u32, u32>(lr, rank, nr, (u32*)nullptr, rank + nr + 1, st);
+    int32_t* dk = keys;
+    u32*     dc = counts;
+    float *  dp = points, *dm = means, *dv = cov;
+    char*    ob = nullptr;
+    if (mem == MMG_MEM_HOST)
+    {
+        const size_t bytes = V * 12 + V * 4 + (points ? V * cap * 12 : 0) + (means ? V * 12 : 0) + (cov ? V * 24 : 0) + 64;
+        ob                 = (char*)m->scratch_get(S_OUT, bytes);
+        if (!ob) return MMG_ERR_OUT_OF_MEM;
+        char* q = ob;
+        if (keys) dk = (int32_t*)q, q += V * 12;
+        if (counts) dc = (u32*)q, q += V * 4;
+        if (points) dp = (float*)q, q += V * cap * 12;
+        if (means) dm = (float*)q, q += V * 12;
+        if (cov) dv = (float*)q, q += V * 24;
+    }
+    const unsigned g = (unsigned)(((size_t)nr * 32 + 255) / 256);
+    if (m->kind == MMG_HASHED_VOXEL)
+        MMG_LAUNCH((k_export<HashedTraits>), g, 256, 0, st, m->dev, nr, rank, dk, dc, dp, (float*)nullptr, (float*)nullptr);
+    else
+        MMG_LAUNCH((k_export<SparseVoxelTraits>), g, 256, 0, st, m->dev, nr, rank, dk, dc, dp, dm, dv);
+    MMG_CUDA(cudaGetLastError());
+    if (mem == MMG_MEM_HOST)
+    {
+        if (keys) MMG_CUDA(cudaMemcpyAsync(keys, dk, V * 12, cudaMemcpyDeviceToHost, st));
+        if (counts) MMG_CUDA(cudaMemcpyAsync(counts, dc, V * 4, cudaMemcpyDeviceToHost, st));
+        if (points) MMG_CUDA(cudaMemcpyAsync(points, dp, V * cap * 12, cudaMemcpyDeviceToHost, st));
+        if (means) MMG_CUDA(cudaMemcpyAsync(means, dm, V * 12, cudaMemcpyDeviceToHost, st));
+        if (cov) MMG_CUDA(cudaMemcpyAsync(cov, dv, V * 24, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaStreamSynchronize(st));
+    }
+    return MMG_OK;
+}
+
+int mmg_num_points(const mmg_map* m, uint64_t* out_n)
+{
+    MMG_CHECK_MAP(m);
+    if (!out_n) return MMG_ERR_INVALID_ARG;
+    if (m->kind == MMG_SPARSE_TREES) return trees_num_points(m, out_n);
+    const u64 V = m->h_nvox_hi - m->h_free_n;
+    *out_n      = 0;
+    if (!V) return MMG_OK;
+    std::vector<u32> c(V);
+    int              rc = export_voxel(m, nullptr, c.data(), nullptr, nullptr, nullptr, MMG_MEM_HOST, 0);
+    if (rc) return rc;
+    u64 s = 0;
+    for (u32 x : c) s += x;
+    *out_n = s;
+    return MMG_OK;
+}
+
+int mmg_export(const mmg_map* m, int32_t* out_keys, uint32_t* out_counts, float* out_points, int mem, void* stream)
+{
+    MMG_CHECK_MAP(m);
+    if (m->kind == MMG_SPARSE_TREES) return trees_export(m, out_keys, out_counts, out_points, mem, (cudaStream_t)stream);
+    return export_voxel(m, out_keys, out_counts, out_points, nullptr, nullptr, mem, (cudaStream_t)stream);
+}
+
+int mmg_voxel_stats(const mmg_map* m, float* out_mean, float* out_cov, int mem, void* stream)
+{
+    MMG_CHECK_MAP(m);
+    if (m->kind != MMG_SPARSE_VOXEL)
+    {
+        set_error("voxel mean/covariance exist for SparseVoxelPointCloud only");
+        return MMG_ERR_UNSUPPORTED;
+    }
+    return export_voxel(m, nullptr, nullptr, nullptr, out_mean, out_cov, mem, (cudaStream_t)stream);
+}
+
+__global__ void k_probe_stats(VoxelMapDev m, u32 nrows, unsigned long long* sum, u32* mx)
+{
+    const u32 vid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (vid >= nrows) return;
+    const u64 key = m.vkey[vid];
+    if (key == KEY_EMPTY) return;
+    u64 h = hash_key(key) & m.mask;
+    u32 len = 1;
+    while (m.table[h].key != key)
+    {
+        h = (h + 1) & m.mask;
+        len++;
+    }
+    atomicAdd(sum, (unsigned long long)len);
+    atomicMax(mx, len);
+}
+
+int mmg_get_table_stats(const mmg_map* cm, mmg_table_stats* out)
+{
+    MMG_CHECK_MAP(cm);
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (!out) return MMG_ERR_INVALID_ARG;
+    memset(out, 0, sizeof(*out));
+    if (m->kind == MMG_SPARSE_TREES) return trees_table_stats(m, out);
+    out->capacity    = m->cap;
+    out->live_voxels = m->h_nvox_hi - m->h_free_n;
+    out->load_factor = m->cap ? (double)out->live_voxels / (double)m->cap : 0;
+    out->hbm_bytes   = m->cap * sizeof(Entry) + m->rowcap * ((u64)m->row_points() * 16 + 4 + 8 + 4 + (m->kind == MMG_SPARSE_VOXEL ? 16 : 0));
+    mmg_num_points(m, &out->points);
+    if (m->h_nvox_hi)
+    {
+        char* b = (char*)m->scratch_get(S_OUT, 64);
+        if (!b) return MMG_ERR_OUT_OF_MEM;
+        MMG_CUDA(cudaMemset(b, 0, 16));
+        MMG_LAUNCH(k_probe_stats, (m->h_nvox_hi + 255) / 256, 256, 0, 0, m->dev, m->h_nvox_hi, (unsigned long long*)b, (u32*)(b + 8));
+        unsigned long long h[2];
+        MMG_CUDA(cudaMemcpy(h, b, 16, cudaMemcpyDeviceToHost));
+        out->mean_probe = out->live_voxels ? (double)h[0] / (double)out->live_voxels : 0;
+        out->max_probe  = (double)(u32)h[1];
+    }
+    return MMG_OK;
+}
+
+int mmg_clone(const mmg_map* src, mmg_map** out)
+{
+    MMG_CHECK_MAP(src);
+    if (!out) return MMG_ERR_INVALID_ARG;
+    MMG_CUDA(cudaDeviceSynchronize());
+    mmg_map* m  = nullptr;
+    int      rc = mmg_create(src->kind, &src->prm, src->device, &m);
+    if (rc) return rc;
+    if (src->kind == MMG_SPARSE_TREES)
+    {
+        rc = trees_clone(src, m);
+    }
+    else
+    {
+        if ((rc = alloc_table(m, src->cap)) == MMG_OK && (rc = ensure_rows(m, src->rowcap ? src->rowcap : 1, 0)) == MMG_OK)
+        {
+            // ensure_rows may round up; copy the source extent only
+            const u64 rc_rows = src->rowcap, cp = (u64)src->row_points();
+            cudaMemcpy(m->dev.table, src->dev.table, src->cap * sizeof(Entry), cudaMemcpyDeviceToDevice);
+            if (rc_rows)
+            {
+                cudaMemcpy(m->dev.pts, src->dev.pts, rc_rows * cp * sizeof(float4), cudaMemcpyDeviceToDevice);
+                cudaMemcpy(m->dev.cnt, src->dev.cnt, rc_rows * sizeof(u32), cudaMemcpyDeviceToDevice);
+                cudaMemcpy(m->dev.vkey, src->dev.vkey, rc_rows * sizeof(u64), cudaMemcpyDeviceToDevice);
+                cudaMemcpy(m->dev.free_list, src->dev.free_list, rc_rows * sizeof(u32), cudaMemcpyDeviceToDevice);
+                if (src->kind == MMG_SPARSE_VOXEL) cudaMemcpy(m->dev.mean, src->dev.mean, rc_rows * sizeof(float4), cudaMemcpyDeviceToDevice);
+            }
+            cudaMemcpy(m->dev.ctr, src->dev.ctr, sizeof(Counters), cudaMemcpyDeviceToDevice);
+            m->h_nvox_hi = src->h_nvox_hi;
+            m->h_free_n  = src->h_free_n;
+            if (cudaGetLastError() != cudaSuccess) rc = MMG_ERR_CUDA;
+        }
+    }
+    if (rc)
+    {
+        mmg_destroy(m);
+        return rc;
+    }
+    *out = m;
+    return MMG_OK;
+}
+
+uint64_t    mmg_kernel_launch_count(void) { return g_launches; }
+const char* mmg_last_error(void) { return g_err; }
+const char* mmg_version(void) { return "mola_b200 maps 0.1 (sm_100a)"; }
+}

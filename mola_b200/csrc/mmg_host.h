@@ -1,0 +1,91 @@
+// mmg_host.h — host-side state behind the opaque mmg_map handle.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <utility>
+#include <vector>
+
+#include "../../include/mola_b200/mmg.h"
+#include "mmg_voxel.cuh"
+
+namespace mmg
+{
+void set_error(const char* fmt, ...);
+#define MMG_CUDA(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t e__ = (expr);                                                              \
+        if (e__ != cudaSuccess)                                                                \
+        {                                                                                      \
+            ::mmg::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            cudaGetLastError();                                                                \
+            return e__ == cudaErrorMemoryAllocation ? MMG_ERR_OUT_OF_MEM : MMG_ERR_CUDA;       \
+        }                                                                                      \
+    } while (0)
+
+enum ScratchSlot
+{
+    S_IN = 0,
+    S_GP,
+    S_VID,
+    S_SORT,
+    S_SEG,
+    S_OUT,
+    S_RCNT,
+    S_ROFF,
+    S_RHITS,
+    S_LIK,
+    S_TREES0,
+    S_TREES1,
+    S_TREES2,
+    S_TREES3,
+    S_COUNT
+};
+struct TreesState;
+}  // namespace mmg
+
+struct mmg_map
+{
+    int        kind = 0, device = 0, num_sms = 148;
+    mmg_params prm{};
+    float      inv = 1.f;
+    // voxel maps
+    mmg::VoxelMapDev dev{};
+    mmg::u64         cap = 0, rowcap = 0;
+    mmg::u32         h_nvox_hi = 0, h_free_n = 0;
+    mmg::Counters*   h_ctr = nullptr;  // pinned mirror
+    bool             points_dirty = false;
+    // radius results of the last mmg_nn_radius_batch
+    mmg::u64  rad_total = 0;
+    mmg::u64* rad_id    = nullptr;
+    float *   rad_xyz = nullptr, *rad_d2 = nullptr;
+    // SparseTrees
+    mmg::TreesState* trees = nullptr;
+    // grow-only device scratch
+    std::vector<std::pair<void*, size_t>> scratch;
+    void*                                 scratch_get(int slot, size_t bytes);
+    int row_points() const { return kind == MMG_SPARSE_VOXEL ? 16 : 32; }
+};
+
+// SparseVoxel radius search (mmg_sv.cu) and SparseTrees (mmg_trees.cu)
+int sv_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float r2, size_t maxp, uint64_t* ooff,
+              uint64_t* ototal, int mem, cudaStream_t st);
+int trees_create(mmg_map* m);
+int trees_destroy(mmg_map* m);
+int trees_clear(mmg_map* m);
+int trees_set_grid(mmg_map* m);
+int trees_clone(const mmg_map* src, mmg_map* dst);
+int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, int has_robot_pose, int mem,
+                 cudaStream_t st);
+int trees_nn_single(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, size_t stride, const double* pose12,
+                    uint8_t* ofound, float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st);
+int trees_nn_multi(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, size_t k, uint32_t* ocount,
+                   float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st);
+int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float r2, size_t maxp,
+                 uint64_t* ooff, uint64_t* ototal, int mem, cudaStream_t st);
+int trees_is_empty(const mmg_map* m, int* out);
+int trees_num_blocks(const mmg_map* m, uint64_t* out);
+int trees_num_points(const mmg_map* m, uint64_t* out);
+int trees_row_capacity(const mmg_map* m, uint32_t* out);
+int trees_export(const mmg_map* m, int32_t* keys, uint32_t* counts, float* points, int mem, cudaStream_t st);
+int trees_bbox_from_points(mmg_map* m);
+int trees_table_stats(mmg_map* m, mmg_table_stats* out);

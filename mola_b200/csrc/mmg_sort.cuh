@@ -1,0 +1,237 @@
+// mmg_sort.cuh — hand-written device primitives: exclusive scan and a stable LSB
+// radix sort of (u32 key, u32 value) pairs. Used to turn "voxel id per point" into
+// per-voxel segments in input order (the reference inserts points sequentially,
+// HashedVoxelPointCloud.cpp:419-422, so per-voxel order is input order).
+#pragma once
+#include "mmg_device.cuh"
+
+namespace mmg
+{
+extern unsigned long long g_launches;  // kernels launched by this library (mmg_kernel_launch_count)
+#define MMG_LAUNCH(kernel, grid, block, smem, stream, ...)              \
+    do {                                                                \
+        kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);     \
+        ++::mmg::g_launches;                                            \
+    } while (0)
+
+// ------------------------------------------------------------------ scan
+constexpr int SCAN_THREADS = 1024, SCAN_ITEMS = 4, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+template <typename T>
+__device__ __forceinline__ T block_exclusive_scan(T v, T* smem /*33*/, T& block_total)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    T         inc  = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        T t = __shfl_up_sync(MMG_FULL, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) smem[warp] = inc;
+    __syncthreads();
+    if (warp == 0)
+    {
+        T w = (lane < nw) ? smem[lane] : 0, wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            T t = __shfl_up_sync(MMG_FULL, wi, o);
+            if (lane >= o) wi += t;
+        }
+        if (lane < nw) smem[lane] = wi - w;  // exclusive warp offsets
+        if (lane == 31) smem[32] = wi;
+    }
+    __syncthreads();
+    const T r   = smem[warp] + inc - v;
+    block_total = smem[32];
+    __syncthreads();
+    return r;
+}
+
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(const TIn* __restrict__ in, size_t n, TOut* __restrict__ bsum)
+{
+    __shared__ TOut sm[33];
+    const size_t    base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+    TOut            s    = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++)
+        if (base + i < n) s += (TOut)in[base + i];
+    TOut tot;
+    block_exclusive_scan<TOut>(s, sm, tot);
+    if (threadIdx.x == 0) bsum[blockIdx.x] = tot;
+}
+template <typename TOut>
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_bsum(TOut* __restrict__ bsum, size_t nb, TOut* __restrict__ total)
+{
+    __shared__ TOut sm[33];
+    TOut            carry = 0;
+    for (size_t b0 = 0; b0 < nb; b0 += SCAN_THREADS)
+    {
+        const size_t i = b0 + threadIdx.x;
+        const TOut   v = (i < nb) ? bsum[i] : 0;
+        TOut         tot;
+        const TOut   e = block_exclusive_scan<TOut>(v, sm, tot);
+        if (i < nb) bsum[i] = carry + e;
+        carry += tot;
+    }
+    if (threadIdx.x == 0 && total) *total = carry;
+}
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(SCAN_THREADS)
+    k_scan_down(const TIn* __restrict__ in, size_t n, const TOut* __restrict__ bsum, TOut* __restrict__ out)
+{
+    __shared__ TOut sm[33];
+    const size_t    base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+    TOut            v[SCAN_ITEMS], s = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++)
+    {
+        v[i] = (base + i < n) ? (TOut)in[base + i] : 0;
+        s += v[i];
+    }
+    TOut tot;
+    TOut e = block_exclusive_scan<TOut>(s, sm, tot) + bsum[blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++)
+    {
+        if (base + i < n) out[base + i] = e;
+        e += v[i];
+    }
+}
+// out[i] = sum_{j<i} in[j] for i in [0,n); *total (device, may be out+n) = sum of all.
+// bsum: scratch of ceil(n/SCAN_TILE) TOut. In-place (in == out, same type) is allowed.
+template <typename TIn, typename TOut>
+inline void exclusive_scan(const TIn* in, TOut* out, size_t n, TOut* total, TOut* bsum, cudaStream_t st)
+{
+    if (n == 0)
+    {
+        if (total) cudaMemsetAsync(total, 0, sizeof(TOut), st);
+        return;
+    }
+    const size_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    MMG_LAUNCH((k_scan_reduce<TIn, TOut>), (unsigned)nb, SCAN_THREADS, 0, st, in, n, bsum);
+    MMG_LAUNCH((k_scan_bsum<TOut>), 1, SCAN_THREADS, 0, st, bsum, nb, total);
+    MMG_LAUNCH((k_scan_down<TIn, TOut>), (unsigned)nb, SCAN_THREADS, 0, st, in, n, bsum, out);
+}
+inline size_t scan_scratch_elems(size_t n) { return (n + SCAN_TILE - 1) / SCAN_TILE + 1; }
+
+// ------------------------------------------------------------ radix sort
+constexpr int RS_THREADS = 256, RS_ITEMS = 16, RS_TILE = RS_THREADS * RS_ITEMS, RS_BITS = 8, RS_RADIX = 1 << RS_BITS;
+constexpr int RS_WARPS = RS_THREADS / 32, RS_WCHUNK = 32 * RS_ITEMS;
+
+static __global__ void __launch_bounds__(RS_THREADS)
+    k_radix_hist(const u32* __restrict__ keys, size_t n, int shift, u32 clampv, u32* __restrict__ ghist, u32 nblocks)
+{
+    __shared__ u32 h[RS_RADIX];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const size_t base = (size_t)blockIdx.x * RS_TILE;
+#pragma unroll 4
+    for (int i = 0; i < RS_ITEMS; i++)
+    {
+        const size_t j = base + (size_t)i * RS_THREADS + threadIdx.x;
+        if (j < n)
+        {
+            const u32 k = min(keys[j], clampv);
+            atomicAdd(&h[(k >> shift) & (RS_RADIX - 1)], 1u);
+        }
+    }
+    __syncthreads();
+    ghist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// Stable scatter. Warp w of the block owns the contiguous chunk
+// [tile + w*512, tile + (w+1)*512); it walks it in 16 rounds of 32 consecutive
+// items, ranking equal digits with __match_any_sync so input order is preserved.
+static __global__ void __launch_bounds__(RS_THREADS)
+    k_radix_scatter(const u32* __restrict__ keys_in, const u32* __restrict__ vals_in /*nullable = iota*/, u32* __restrict__ keys_out,
+                    u32* __restrict__ vals_out, size_t n, int shift, u32 clampv, const u32* __restrict__ gscan, u32 nblocks)
+{
+    __shared__ u32 wcnt[RS_WARPS][RS_RADIX];
+    const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&wcnt[0][0])[i] = 0;
+    __syncthreads();
+    const size_t   wbase = (size_t)blockIdx.x * RS_TILE + (size_t)warp * RS_WCHUNK;
+    u32            key[RS_ITEMS];
+    unsigned short rank[RS_ITEMS];
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; r++)
+    {
+        const size_t j     = wbase + (size_t)r * 32 + lane;
+        const bool   valid = j < n;
+        key[r]             = valid ? min(keys_in[j], clampv) : 0xFFFFFFFFu;
+        const u32 digit    = (key[r] >> shift) & (RS_RADIX - 1);
+        // lanes past the end form their own group (digit 256) so they never disturb ranks
+        const u32 peers  = __match_any_sync(MMG_FULL, valid ? digit : (u32)RS_RADIX);
+        const int leader = __ffs(peers) - 1;
+        u32       base   = 0;
+        if (valid && lane == leader)
+        {
+            base = wcnt[warp][digit];
+            wcnt[warp][digit] = base + __popc(peers);
+        }
+        base    = __shfl_sync(MMG_FULL, base, leader);
+        rank[r] = (unsigned short)(base + __popc(peers & ((1u << lane) - 1)));
+        __syncwarp();
+    }
+    __syncthreads();
+    {  // thread d turns the per-warp counts of digit d into global output offsets
+        const int d   = threadIdx.x;
+        u32       run = gscan[(size_t)d * nblocks + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++)
+        {
+            const u32 c = wcnt[w][d];
+            wcnt[w][d]  = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; r++)
+    {
+        const size_t j = wbase + (size_t)r * 32 + lane;
+        if (j < n)
+        {
+            const u32    digit = (key[r] >> shift) & (RS_RADIX - 1);
+            const size_t pos   = (size_t)wcnt[warp][digit] + rank[r];
+            keys_out[pos]      = key[r];
+            vals_out[pos]      = vals_in ? vals_in[j] : (u32)j;
+        }
+    }
+}
+
+struct SortScratch
+{
+    u32 *keys_b, *vals_a, *vals_b, *ghist, *bsum;  // keys_b/vals_*: n each; ghist: 256*nblocks; bsum: scan scratch
+};
+inline size_t sort_nblocks(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
+
+// Sorts keys (clamped to clampv) ascending, stable, carrying the original index
+// as value. Returns pointers to the sorted keys / indices (inside scratch or keys).
+inline void radix_sort_index(u32* keys, size_t n, u32 clampv, const SortScratch& s, u32** sorted_keys, u32** sorted_idx,
+                             cudaStream_t st)
+{
+    int bits = 1;
+    while (bits < 32 && (clampv >> bits) != 0) bits++;
+    const int passes = (bits + RS_BITS - 1) / RS_BITS;
+    const u32 nb     = (u32)sort_nblocks(n);
+    u32 *     kin = keys, *kout = s.keys_b, *vin = nullptr, *vout = s.vals_a;
+    for (int p = 0; p < passes; p++)
+    {
+        const int shift = p * RS_BITS;
+        MMG_LAUNCH(k_radix_hist, nb, RS_THREADS, 0, st, kin, n, shift, clampv, s.ghist, nb);
+        exclusive_scan<u32, u32>(s.ghist, s.ghist, (size_t)RS_RADIX * nb, nullptr, s.bsum, st);
+        MMG_LAUNCH(k_radix_scatter, nb, RS_THREADS, 0, st, kin, vin, kout, vout, n, shift, clampv, s.ghist, nb);
+        u32* t = kin;
+        kin    = kout;
+        kout   = t;
+        vin    = vout;
+        vout   = (vout == s.vals_a) ? s.vals_b : s.vals_a;
+    }
+    *sorted_keys = kin;
+    *sorted_idx  = vin;
+}
+}  // namespace mmg
