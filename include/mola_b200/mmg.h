@@ -114,7 +114,7 @@ int mmg_insert_batch(mmg_map* m, const float* xs, const float* ys, const float* 
                      const double* pose12, int has_robot_pose, int mem, void* stream);
 
 /* out_found[n] (0/1), out_xyz[n*3], out_d2[n], out_id[n]. Entries of not-found
- * queries are left untouched except out_found. */
+ * queries are zero. */
 int mmg_nn_single_batch(const mmg_map* m, const float* xs, const float* ys, const float* zs,
                         size_t n, const double* pose12, uint8_t* out_found, float* out_xyz,
                         float* out_d2, uint64_t* out_id, int mem, void* stream);
@@ -163,6 +163,11 @@ typedef struct mmg_table_stats
     double   load_factor, mean_probe, max_probe;
 } mmg_table_stats;
 int mmg_get_table_stats(const mmg_map* m, mmg_table_stats* out);
+
+/* Diagnostics: mean number of stored points in the 27-cell stencil of the queries
+ * (P-bar of the roofline's algorithmic-bytes formula). Voxel maps only. */
+int mmg_mean_stencil_points(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n,
+                            int mem, void* stream, double* out);
 
 /* Multi-GPU: replicate a built map from `root` to every rank over NCCL. */
 int mmg_comm_unique_id(uint8_t out_id[128]);

@@ -27,7 +27,7 @@ void set_error(const char* fmt, ...)
 using namespace mmg;
 
 // ------------------------------------------------------------------ helpers
-static PoseD make_pose(const double* pose12)
+PoseD mmg::make_pose(const double* pose12)
 {
     PoseD              T;
     static const double I[12] = {1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0};
@@ -79,7 +79,7 @@ static int init_counters(mmg_map* m, bool keep_bbox)
     return MMG_OK;
 }
 
-static int alloc_table(mmg_map* m, u64 cap)
+int mmg::alloc_table(mmg_map* m, u64 cap)
 {
     Entry* t = nullptr;
     if (cudaMalloc(&t, cap * sizeof(Entry)) != cudaSuccess)
@@ -128,7 +128,7 @@ static int grow_array(T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
     return MMG_OK;
 }
 
-static int ensure_rows(mmg_map* m, u64 rows, cudaStream_t st)
+int mmg::ensure_rows(mmg_map* m, u64 rows, cudaStream_t st)
 {
     if (rows <= m->rowcap) return MMG_OK;
     const u64 newcap = std::max<u64>(rows + rows / 2, 4096);
@@ -143,7 +143,7 @@ static int ensure_rows(mmg_map* m, u64 rows, cudaStream_t st)
     return MMG_OK;
 }
 
-static int read_counters(mmg_map* m, Counters* c, cudaStream_t st)
+int mmg::read_counters(mmg_map* m, Counters* c, cudaStream_t st)
 {
     MMG_CUDA(cudaMemcpyAsync(m->h_ctr, m->dev.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
     MMG_CUDA(cudaStreamSynchronize(st));
@@ -152,7 +152,7 @@ static int read_counters(mmg_map* m, Counters* c, cudaStream_t st)
 }
 
 // Stages caller SoA inputs on the device when they live in host memory.
-static int stage_in(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, int mem, cudaStream_t st, const float** dx,
+int mmg::stage_in(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, int mem, cudaStream_t st, const float** dx,
                     const float** dy, const float** dz)
 {
     if (mem == MMG_MEM_DEVICE)
@@ -169,7 +169,7 @@ static int stage_in(mmg_map* m, const float* xs, const float* ys, const float* z
     return MMG_OK;
 }
 
-static unsigned persistent_blocks(const mmg_map* m, size_t work_warps, int warps_per_block, int blocks_per_sm)
+unsigned mmg::persistent_blocks(const mmg_map* m, size_t work_warps, int warps_per_block, int blocks_per_sm)
 {
     const size_t need = (work_warps + warps_per_block - 1) / warps_per_block;
     return (unsigned)std::max<size_t>(1, std::min<size_t>(need, (size_t)m->num_sms * blocks_per_sm));
@@ -841,6 +841,51 @@ int mmg_clone(const mmg_map* src, mmg_map** out)
         return rc;
     }
     *out = m;
+    return MMG_OK;
+}
+
+__global__ void k_stencil_points(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, float inv,
+                                 int round_mode, unsigned long long* total)
+{
+    const u32 q = blockIdx.x * blockDim.x + threadIdx.x;
+    u32       s = 0;
+    if (q < n)
+    {
+        int  c[3];
+        bool ok = round_mode ? (SparseVoxelTraits::to_index(qx[q], inv, c[0]) & SparseVoxelTraits::to_index(qy[q], inv, c[1]) & SparseVoxelTraits::to_index(qz[q], inv, c[2]))
+                             : (HashedTraits::to_index(qx[q], inv, c[0]) & HashedTraits::to_index(qy[q], inv, c[1]) & HashedTraits::to_index(qz[q], inv, c[2]));
+        if (ok)
+            for (int x = c[0] - 1; x <= c[0] + 1; x++)
+                for (int y = c[1] - 1; y <= c[1] + 1; y++)
+                    for (int z = c[2] - 1; z <= c[2] + 1; z++)
+                    {
+                        u32 vid, cnt;
+                        if (index_in_range(x, y, z) && probe_ro(m.table, m.mask, pack_key(x, y, z), vid, cnt)) s += cnt;
+                    }
+    }
+    s = __reduce_add_sync(MMG_FULL, s);
+    if ((threadIdx.x & 31) == 0 && s) atomicAdd(total, (unsigned long long)s);
+}
+
+int mmg_mean_stencil_points(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, int mem, void* stream, double* out)
+{
+    MMG_CHECK_MAP(cm);
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (!out || m->kind == MMG_SPARSE_TREES) return MMG_ERR_INVALID_ARG;
+    *out = 0;
+    if (!n) return MMG_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    unsigned long long* d = (unsigned long long*)m->scratch_get(S_LIK, 64);
+    if (!d) return MMG_ERR_OUT_OF_MEM;
+    MMG_CUDA(cudaMemsetAsync(d, 0, 8, st));
+    MMG_LAUNCH(k_stencil_points, (unsigned)((n + 255) / 256), 256, 0, st, m->dev, dx, dy, dz, (u32)n, m->inv, m->kind == MMG_SPARSE_VOXEL ? 1 : 0, d);
+    unsigned long long h = 0;
+    MMG_CUDA(cudaMemcpyAsync(&h, d, 8, cudaMemcpyDeviceToHost, st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    *out = (double)h / (double)n;
     return MMG_OK;
 }
 

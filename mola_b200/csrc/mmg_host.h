@@ -89,3 +89,14 @@ int trees_row_capacity(const mmg_map* m, uint32_t* out);
 int trees_export(const mmg_map* m, int32_t* keys, uint32_t* counts, float* points, int mem, cudaStream_t st);
 int trees_bbox_from_points(mmg_map* m);
 int trees_table_stats(mmg_map* m, mmg_table_stats* out);
+
+namespace mmg
+{
+int      alloc_table(mmg_map* m, u64 cap);
+int      ensure_rows(mmg_map* m, u64 rows, cudaStream_t st);
+int      read_counters(mmg_map* m, Counters* c, cudaStream_t st);
+int      stage_in(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, int mem, cudaStream_t st, const float** dx, const float** dy,
+                  const float** dz);
+PoseD    make_pose(const double* pose12);
+unsigned persistent_blocks(const mmg_map* m, size_t work_warps, int warps_per_block, int blocks_per_sm);
+}  // namespace mmg

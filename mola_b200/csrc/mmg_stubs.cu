@@ -19,9 +19,6 @@ int trees_row_capacity(const mmg_map*, uint32_t* o) { *o = 0; return MMG_OK; }
 int trees_export(const mmg_map*, int32_t*, uint32_t*, float*, int, cudaStream_t) UNSUP("trees")
 int trees_bbox_from_points(mmg_map*) UNSUP("trees")
 int trees_table_stats(mmg_map*, mmg_table_stats*) UNSUP("trees")
-extern "C" {
-int mmg_comm_unique_id(uint8_t*) UNSUP("nccl")
-int mmg_comm_init(const uint8_t*, int, int, int, mmg_comm**) UNSUP("nccl")
-int mmg_comm_destroy(mmg_comm*) UNSUP("nccl")
-int mmg_bcast(mmg_map*, mmg_comm*, int, void*) UNSUP("nccl")
+namespace mmg {
+int trees_bcast(mmg_map*, int, int, void*, cudaStream_t, u64, u64, int (*)(void*, void*, size_t, int, cudaStream_t)) UNSUP("trees")
 }

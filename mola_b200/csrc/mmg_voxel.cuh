@@ -489,7 +489,16 @@ __global__ void __launch_bounds__(256)
                 rr = orr;
             }
         }
-        if (lane == 0) out.found[q] = (rr != 0xFFFFFFFFu) ? 1 : 0;
+        if (lane == 0)
+        {
+            out.found[q] = (rr != 0xFFFFFFFFu) ? 1 : 0;
+            if (rr == 0xFFFFFFFFu)
+            {
+                out.xyz[3 * (size_t)q] = 0.f, out.xyz[3 * (size_t)q + 1] = 0.f, out.xyz[3 * (size_t)q + 2] = 0.f;
+                out.d2[q] = 0.f;
+                out.id[q] = 0;
+            }
+        }
         if (rr != 0xFFFFFFFFu && br == rr)
         {
             const int b = (int)(rr >> 5), slot = (int)(rr & 31);
