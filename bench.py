@@ -1,0 +1,370 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the hot path (BASELINE.json config 2).
+
+Workload: a ~10M-point HashedVoxelPointCloud (voxel 0.5 m, cap 32/voxel) built by inserting
+synthetic HDL-64 scans along a procedural street, then batched nn_single_search of 1M query
+points (9 consecutive re-posed scans, truncated) per step. One step = one pass of 1M queries.
+
+  value  : queries/s with queries resident in HBM (device pointers through the C ABI)
+  e2e    : queries/s through the C ABI with HOST (pinned) buffers, H2D + D2H inside the timed region
+  roofline / cpu_baseline / clocks: see DESIGN.md "Measurement"
+
+`--impl reference` times the reference's own CPU code (oracle/_ref when it was built, else the
+oracle port) on the same map and a bounded sample of the same queries.
+Under torchrun (N>1): rank 0 builds the map, broadcasts it with NCCL, every rank queries its own
+1M-point batch (weak scaling); time = max over ranks.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+VOXEL = 0.5
+MAP_POINTS = 10_000_000
+N_QUERIES = 1_000_000
+SPACING = 5.0          # metres between map scans
+MAX_SCANS = 900
+
+
+def compose_host(pose12, xs, ys, zs):
+    T = np.asarray(pose12, np.float64)
+    x, y, z = xs.astype(np.float64), ys.astype(np.float64), zs.astype(np.float64)
+    return [(((T[3 * r] * x + T[3 * r + 1] * y) + T[3 * r + 2] * z) + T[9 + r]).astype(np.float32) for r in range(3)]
+
+
+def map_scans(target_points, count_fn, insert_fn, log=None):
+    """Feeds scans to insert_fn until count_fn() >= target_points. Returns (#scans, #input points)."""
+    from mola_b200 import synth
+    n_in, k = 0, 0
+    while k < MAX_SCANS:
+        xs, ys, zs, pose = synth.lidar_scan("hdl64", s=SPACING * k, seed=2, scan_id=k)
+        insert_fn(xs, ys, zs, pose)
+        n_in += xs.size
+        k += 1
+        if k % 16 == 0 or k < 4:
+            c = count_fn()
+            if log:
+                log(f"  scan {k}: {c} stored points")
+            if c >= target_points:
+                break
+    return k, n_in
+
+
+def query_batch(n_scans_in_map, rank=0, n=N_QUERIES):
+    """n query points in the map frame: consecutive scans taken mid-trajectory, each re-posed by a
+    small SE(3) step (one ICP iteration's pose guess), truncated to n."""
+    from mola_b200 import synth
+    out = [[], [], []]
+    have, j = 0, 0
+    s0 = SPACING * (n_scans_in_map // 2) + 1.7 + 50.0 * rank
+    while have < n:
+        xs, ys, zs, pose = synth.lidar_scan("hdl64", s=s0 + 1.0 * j, seed=2, scan_id=100000 + 1000 * rank + j)
+        g = compose_host(synth.perturbed_pose(pose), xs, ys, zs)
+        for a in range(3):
+            out[a].append(g[a])
+        have += xs.size
+        j += 1
+    return [np.ascontiguousarray(np.concatenate(o)[:n]) for o in out]
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def cpu_threads():
+    return max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
+
+
+def cpu_lib_kind():
+    from oracle import mmo
+    return "reference" if mmo.have_reference() else "port"
+
+
+def time_cpu_queries(omap, q, sample, threads, repeats=3):
+    """queries/s of the CPU checker on the first `sample` queries, best of `repeats`."""
+    best = None
+    for _ in range(repeats):
+        t = time.perf_counter()
+        omap.nn_single(q[0][:sample], q[1][:sample], q[2][:sample], nthreads=threads)
+        dt = time.perf_counter() - t
+        best = dt if best is None else min(best, dt)
+    return sample / best, best
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the same path on the host cores."""
+    if rank != 0:
+        return
+    from oracle import mmo
+    kind = cpu_lib_kind()
+    log = (lambda s: print(s, file=sys.stderr, flush=True)) if args.verbose else None
+    om = mmo.OracleMap(0, VOXEL, which=kind)
+    t0 = time.perf_counter()
+    ins_t = [0.0]
+
+    def ins(xs, ys, zs, pose):
+        t = time.perf_counter()
+        om.insert(xs, ys, zs, pose)
+        ins_t[0] += time.perf_counter() - t
+    nscans, n_in = map_scans(args.map_points, om.num_points, ins, log)
+    q = query_batch(nscans)
+    threads = cpu_threads()
+    sample = min(N_QUERIES, args.cpu_sample)
+    for _ in range(args.warmup):
+        om.nn_single(q[0][:sample], q[1][:sample], q[2][:sample], nthreads=threads)
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        om.nn_single(q[0][:sample], q[1][:sample], q[2][:sample], nthreads=threads)
+    dt = time.perf_counter() - t
+    qps = sample * args.steps / dt
+    qps1, _ = time_cpu_queries(om, q, min(sample, 100_000), 1, repeats=2)
+    line = {"impl": "reference", "metric": "nn_single_search queries/s", "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C2: 10M-pt HashedVoxelPointCloud (voxel 0.5 m), batched nn_single_search", "map_points": int(om.num_points()),
+                       "map_voxels": int(om.num_voxels()), "queries_per_step": sample, "map_scans": nscans},
+            "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": threads, "kind": kind,
+                             "sample": f"{sample} of the 1M queries per step, {threads} threads; 1 thread: {qps1:.0f} q/s",
+                             "value_1thread": qps1, "insert_mpts_s_1thread": n_in / ins_t[0] / 1e6},
+            "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "setup_s": time.perf_counter() - t0}
+    print(json.dumps(line), flush=True)
+
+
+def run_gpu(args, rank, world, local_rank):
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from mola_b200 import HashedVoxelPointCloud, capi
+    from mola_b200.maps import Communicator
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    log = (lambda s: print(s, file=sys.stderr, flush=True)) if (args.verbose and rank == 0) else None
+    lib = capi.lib()
+    t_setup = time.perf_counter()
+    gmap = HashedVoxelPointCloud(VOXEL, device=local_rank)
+    stream = torch.cuda.current_stream(dev)
+    sp = C.c_void_p(stream.cuda_stream)
+
+    # ---- map build (rank 0), CPU twin for the cpu_baseline leg (rank 0, N == 1) ----------------
+    want_cpu = (rank == 0 and world == 1 and not args.no_cpu)
+    om = None
+    if want_cpu:
+        from oracle import mmo
+        cpu_kind = cpu_lib_kind()
+        om = mmo.OracleMap(0, VOXEL, which=cpu_kind)
+    ins_ms, cpu_ins_s, nscans, n_in = [0.0], [0.0], 0, 0
+    if rank == 0:
+        def ins(xs, ys, zs, pose):
+            dx, dy, dz = (torch.from_numpy(a).to(dev) for a in (xs, ys, zs))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            gmap.insertPointCloud(dx, dy, dz, pose)
+            e1.record(stream)
+            e1.synchronize()
+            ins_ms[0] += e0.elapsed_time(e1)
+            if om is not None:
+                t = time.perf_counter()
+                om.insert(xs, ys, zs, pose)
+                cpu_ins_s[0] += time.perf_counter() - t
+        nscans, n_in = map_scans(args.map_points, gmap.numPoints, ins, log)
+    if world > 1:
+        obj = [Communicator.unique_id() if rank == 0 else None, nscans]
+        dist.broadcast_object_list(obj, src=0)
+        comm = Communicator(obj[0], rank, world, local_rank)
+        nscans = obj[1]
+        torch.cuda.synchronize()
+        tb = time.perf_counter()
+        gmap.broadcast(comm, 0)
+        torch.cuda.synchronize()
+        bcast_s = time.perf_counter() - tb
+    else:
+        bcast_s = 0.0
+    stats = gmap.tableStats()
+
+    # ---- queries ---------------------------------------------------------------------------
+    q = query_batch(nscans, rank)
+    n = q[0].size
+    hq = [torch.from_numpy(a).pin_memory() for a in q]                       # pinned host inputs
+    dq = [a.to(dev, non_blocking=True) for a in hq]                          # HBM-resident inputs
+    d_found = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_xyz = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    d_d2 = torch.empty(n, dtype=torch.float32, device=dev)
+    d_id = torch.empty(n, dtype=torch.int64, device=dev)
+    h_found = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h_xyz = torch.empty((n, 3), dtype=torch.float32).pin_memory()
+    h_d2 = torch.empty(n, dtype=torch.float32).pin_memory()
+    h_id = torch.empty(n, dtype=torch.int64).pin_memory()
+    fp = lambda t: C.cast(t.data_ptr(), C.POINTER(C.c_float))
+    vp = lambda t: C.c_void_p(t.data_ptr())
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)            # > 126 MB L2
+
+    def step_device():
+        capi.check(lib.mmg_nn_single_batch(gmap._h, fp(dq[0]), fp(dq[1]), fp(dq[2]), C.c_size_t(n), None, vp(d_found), vp(d_xyz), vp(d_d2),
+                                           vp(d_id), capi.MEM_DEVICE, sp))
+
+    def step_host():
+        capi.check(lib.mmg_nn_single_batch(gmap._h, fp(hq[0]), fp(hq[1]), fp(hq[2]), C.c_size_t(n), None, vp(h_found), vp(h_xyz), vp(h_d2),
+                                           vp(h_id), capi.MEM_HOST, sp))
+
+    pbar = C.c_double()
+    capi.check(lib.mmg_mean_stencil_points(gmap._h, fp(dq[0]), fp(dq[1]), fp(dq[2]), C.c_size_t(n), capi.MEM_DEVICE, sp, C.byref(pbar)))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.mmg_kernel_launch_count()
+    evs = []
+    t_wall = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        step_device()
+        e1.record(stream)
+        evs.append((e0, e1))
+    barrier()
+    wall_s = time.perf_counter() - t_wall
+    launches = lib.mmg_kernel_launch_count() - launches0
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    # ---- end to end: host buffers through the C ABI -------------------------------------------
+    for _ in range(2):
+        step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_host()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    found_frac = float(d_found.float().mean().item())
+
+    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        return
+    total_q = n * world
+    qps = total_q * args.steps / (dev_ms * 1e-3)
+    e2e_qps = total_q * args.steps / (e2e_ms * 1e-3)
+    # roofline: algorithmic bytes per query = 361 + 12 * P-bar; one launch = one step
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    bytes_per_q = 361.0 + 12.0 * pbar.value
+    achieved = bytes_per_q * n / (dev_ms / args.steps * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("k_nn_single_dram_bytes_per_launch")
+    except Exception:
+        pass
+    line = {"metric": "nn_single_search queries/s", "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C2: 10M-pt HashedVoxelPointCloud (voxel 0.5 m), batched nn_single_search of 1M points per step per GPU",
+                       "map_points": int(stats["points"]), "map_voxels": int(stats["live_voxels"]), "map_scans": nscans,
+                       "queries_per_step_per_gpu": n, "l2": "flushed between steps (256 MiB write)", "map_hbm_bytes": int(stats["hbm_bytes"]),
+                       "parallelism": f"map replicated by NCCL broadcast, queries sharded x{world}"},
+            "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": 12 * n, "d2h_bytes_per_step": 25 * n},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "kernel": "k_nn_single<HashedTraits>", "algorithmic_bytes_per_query": bytes_per_q, "mean_stencil_points": pbar.value,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650"},
+            "clocks": clocks, "found_frac": found_frac, "wall_ms_per_step_incl_flush": 1e3 * wall_s / args.steps,
+            "insert": {"mpts_s": n_in / (ins_ms[0] * 1e-3) / 1e6 if ins_ms[0] else None, "points_in": n_in, "scans": nscans,
+                       "note": "per-scan batches of 120k points, device-resident inputs, CUDA-event time"},
+            "table": {k: stats[k] for k in ("capacity", "load_factor", "mean_probe", "max_probe")},
+            "bcast_s": bcast_s, "setup_s": time.perf_counter() - t_setup}
+    if om is not None:
+        threads = cpu_threads()
+        sample = min(n, args.cpu_sample)
+        qps_mt, _ = time_cpu_queries(om, q, sample, threads, repeats=2)
+        qps_1, _ = time_cpu_queries(om, q, min(sample, 100_000), 1, repeats=2)
+        line["cpu_baseline"] = {"value": qps_mt, "unit": "queries/s", "cores": threads, "kind": cpu_kind,
+                                "sample": f"first {sample} of the 1M queries on the same 10M-pt map, {threads} threads (1 thread: {qps_1:.0f} q/s)",
+                                "value_1thread": qps_1, "insert_mpts_s_1thread": n_in / cpu_ins_s[0] / 1e6 if cpu_ins_s[0] else None}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--map-points", type=int, default=MAP_POINTS)
+    ap.add_argument("--cpu-sample", type=int, default=200_000)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--verbose", action="store_true")
+    args = ap.parse_args()
+    rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the map kernels have no CPU fallback")
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_gpu(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

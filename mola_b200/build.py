@@ -15,7 +15,7 @@ CSRC = os.path.join(ROOT, "mola_b200", "csrc")
 LIBDIR = os.path.join(ROOT, "mola_b200", "_lib")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "--extended-lambda", "-Xcompiler", "-fPIC", "-shared", "-cudart", "shared"]
+              "--extended-lambda", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared", "-cudart", "shared"]
 
 
 def _newer(target, sources):

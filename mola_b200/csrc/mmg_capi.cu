@@ -4,11 +4,13 @@
 // is deliberately no CPU path: without a CUDA device mmg_create fails.
 #include "../../include/mola_b200/mmg.h"
 #include "mmg_host.h"
+#include "mmg_query.cuh"
 
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -281,8 +283,17 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
         o.id = (u64*)ob, o.xyz = (float*)(ob + nq * 8), o.d2 = (float*)(ob + nq * 20), o.found = (uint8_t*)(ob + nq * 24);
     }
     const PoseD    T  = make_pose(pose12);
-    const unsigned nb = persistent_blocks(m, nq, 8, 8);
-    MMG_LAUNCH((k_nn_single<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, o);
+    static const bool simple = getenv("MMG_NN_SIMPLE") != nullptr;  // A/B switch: one warp per query, no grouping
+    if (simple)
+    {
+        const unsigned nb = persistent_blocks(m, nq, 8, 8);
+        MMG_LAUNCH((k_nn_single<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, o);
+    }
+    else
+    {
+        const unsigned nb = persistent_blocks(m, (nq + 31) / 32, 8, 8);
+        MMG_LAUNCH((k_nn_single_grouped<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, o);
+    }
     MMG_CUDA(cudaGetLastError());
     if (mem == MMG_MEM_HOST)
     {
