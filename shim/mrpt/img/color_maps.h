@@ -1,0 +1,2 @@
+#pragma once
+#include "../mrpt_min.h"
