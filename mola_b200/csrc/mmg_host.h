@@ -33,6 +33,10 @@ enum ScratchSlot
     S_RCNT,
     S_ROFF,
     S_RHITS,
+    S_RHITS2,
+    S_HWORK,
+    S_HSORT,
+    S_QID,
     S_LIK,
     S_TREES0,
     S_TREES1,

@@ -209,16 +209,22 @@ struct SortScratch
 };
 inline size_t sort_nblocks(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
 
-// Sorts keys (clamped to clampv) ascending, stable, carrying the original index
-// as value. Returns pointers to the sorted keys / indices (inside scratch or keys).
-inline void radix_sort_index(u32* keys, size_t n, u32 clampv, const SortScratch& s, u32** sorted_keys, u32** sorted_idx,
+// Sorts keys (clamped to clampv) ascending, stable, carrying a u32 value per key:
+// vals_in == nullptr means the original index (iota), otherwise the caller's values
+// (e.g. the permutation of a previous sort, which chains several stable sorts into
+// one multi-key sort). vals_in may be s.vals_a or s.vals_b (the result of a previous
+// call with the same scratch). Returns pointers to the sorted keys / values (inside
+// the scratch or `keys`, which is clobbered).
+inline void radix_sort_pairs(u32* keys, const u32* vals_in, size_t n, u32 clampv, const SortScratch& s, u32** sorted_keys, u32** sorted_vals,
                              cudaStream_t st)
 {
     int bits = 1;
     while (bits < 32 && (clampv >> bits) != 0) bits++;
-    const int passes = (bits + RS_BITS - 1) / RS_BITS;
-    const u32 nb     = (u32)sort_nblocks(n);
-    u32 *     kin = keys, *kout = s.keys_b, *vin = nullptr, *vout = s.vals_a;
+    const int  passes = (bits + RS_BITS - 1) / RS_BITS;
+    const u32  nb     = (u32)sort_nblocks(n);
+    u32 *      kin = keys, *kout = s.keys_b;
+    const u32* vin  = vals_in;
+    u32*       vout = (vals_in == s.vals_a) ? s.vals_b : s.vals_a;
     for (int p = 0; p < passes; p++)
     {
         const int shift = p * RS_BITS;
@@ -232,6 +238,21 @@ inline void radix_sort_index(u32* keys, size_t n, u32 clampv, const SortScratch&
         vout   = (vout == s.vals_a) ? s.vals_b : s.vals_a;
     }
     *sorted_keys = kin;
-    *sorted_idx  = vin;
+    *sorted_vals = const_cast<u32*>(vin);
+}
+inline void radix_sort_index(u32* keys, size_t n, u32 clampv, const SortScratch& s, u32** sorted_keys, u32** sorted_idx, cudaStream_t st)
+{
+    radix_sort_pairs(keys, nullptr, n, clampv, s, sorted_keys, sorted_idx, st);
+}
+// u32 words a SortScratch needs for n items (keys_b, vals_a, vals_b, ghist, bsum)
+inline size_t sort_scratch_words(size_t n)
+{
+    const size_t nb = sort_nblocks(n);
+    return 3 * n + (size_t)RS_RADIX * nb + scan_scratch_elems((size_t)RS_RADIX * nb);
+}
+inline SortScratch sort_scratch_at(u32* base, size_t n)
+{
+    const size_t nb = sort_nblocks(n);
+    return SortScratch{base, base + n, base + 2 * n, base + 3 * n, base + 3 * n + (size_t)RS_RADIX * nb};
 }
 }  // namespace mmg

@@ -2,7 +2,6 @@
 #include "mmg_host.h"
 using namespace mmg;
 #define UNSUP(name) { set_error(name ": not implemented yet"); return MMG_ERR_UNSUPPORTED; }
-int sv_radius(mmg_map*, const float*, const float*, const float*, size_t, const double*, float, size_t, uint64_t*, uint64_t*, int, cudaStream_t) UNSUP("sv_radius")
 int trees_create(mmg_map*) { return MMG_OK; }
 int trees_destroy(mmg_map*) { return MMG_OK; }
 int trees_clear(mmg_map*) UNSUP("trees")
