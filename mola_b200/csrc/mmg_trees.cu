@@ -1,0 +1,632 @@
+// mmg_trees.cu — host side of the SparseTreesPointCloud flavour (kernels: mmg_trees.cuh).
+// Reference behaviour: mola_metric_maps/src/SparseTreesPointCloud.cpp:298-307 (insertObservation +
+// eraseGridsFartherThan :961-1000), :916-959 (internal_insertPointCloud3D), :613-713 (queries),
+// :715-741 (boundingBox).
+#include "mmg_hits.cuh"
+#include "mmg_trees.cuh"
+
+#include <cmath>
+#include <cstring>
+
+using namespace mmg;
+
+namespace mmg
+{
+struct TreesState
+{
+    TreesDev       dev{};
+    u64            bcap = 0, brows = 0, ccap = 0, crows = 0;
+    u32            brow_hi = 0, bfree_n = 0, crow_hi = 0, cfree_n = 0, ncells = 0;
+    u64            npoints = 0;
+    TreesCounters* h_ctr   = nullptr;  // pinned mirror
+};
+}  // namespace mmg
+
+namespace
+{
+template <typename T>
+int grow(T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
+{
+    T* q = nullptr;
+    if (cudaMalloc(&q, newn * sizeof(T)) != cudaSuccess)
+    {
+        set_error("cudaMalloc(%llu B) failed", (unsigned long long)(newn * sizeof(T)));
+        cudaGetLastError();
+        return MMG_ERR_OUT_OF_MEM;
+    }
+    if (oldn) MMG_CUDA(cudaMemcpyAsync(q, *p, oldn * sizeof(T), cudaMemcpyDeviceToDevice, st));
+    MMG_CUDA(cudaMemsetAsync(q + oldn, fill_byte, (newn - oldn) * sizeof(T), st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    if (*p) cudaFree(*p);
+    *p = q;
+    return MMG_OK;
+}
+int new_table(Entry** tab, u64 cap)
+{
+    Entry* t = nullptr;
+    if (cudaMalloc(&t, cap * sizeof(Entry)) != cudaSuccess)
+    {
+        set_error("cudaMalloc table (%llu entries) failed", (unsigned long long)cap);
+        cudaGetLastError();
+        return MMG_ERR_OUT_OF_MEM;
+    }
+    MMG_CUDA(cudaMemset(t, 0xFF, cap * sizeof(Entry)));
+    *tab = t;
+    return MMG_OK;
+}
+u64 pow2_for(u64 entries, u64 minimum)
+{
+    u64 cap = minimum;
+    while (cap < 2 * entries) cap <<= 1;
+    return cap;
+}
+int read_ctr(mmg_map* m, cudaStream_t st)
+{
+    TreesState* s = m->trees;
+    MMG_CUDA(cudaMemcpyAsync(s->h_ctr, s->dev.ctr, sizeof(TreesCounters), cudaMemcpyDeviceToHost, st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    s->brow_hi = s->h_ctr->brow_hi, s->bfree_n = s->h_ctr->bfree_n, s->crow_hi = s->h_ctr->crow_hi, s->cfree_n = s->h_ctr->cfree_n;
+    s->ncells = s->h_ctr->ncells, s->npoints = s->h_ctr->npoints;
+    return MMG_OK;
+}
+int ensure_block_rows(mmg_map* m, u64 rows, cudaStream_t st)
+{
+    TreesState* s = m->trees;
+    if (rows <= s->brows) return MMG_OK;
+    const u64 nc = std::max<u64>(rows + rows / 2, 256);
+    int       rc;
+    if ((rc = grow(&s->dev.bkey, s->brows, nc, 0xFF, st))) return rc;
+    if ((rc = grow(&s->dev.bcnt, s->brows, nc, 0, st))) return rc;
+    if ((rc = grow(&s->dev.l1, s->brows * 16, nc * 16, 0, st))) return rc;
+    if ((rc = grow(&s->dev.l0, s->brows * 1024, nc * 1024, 0, st))) return rc;
+    if ((rc = grow(&s->dev.bfree, s->brows, nc, 0, st))) return rc;
+    s->brows = nc;
+    return MMG_OK;
+}
+int ensure_chain_rows(mmg_map* m, u64 rows, cudaStream_t st)
+{
+    TreesState* s = m->trees;
+    if (rows <= s->crows) return MMG_OK;
+    const u64 nc = std::max<u64>(rows + rows / 2, 4096);
+    int       rc;
+    if ((rc = grow(&s->dev.cpts, s->crows * TR_ROW, nc * TR_ROW, 0, st))) return rc;
+    if ((rc = grow(&s->dev.cnext, s->crows, nc, 0xFF, st))) return rc;
+    if ((rc = grow(&s->dev.cfree, s->crows, nc, 0, st))) return rc;
+    s->crows = nc;
+    return MMG_OK;
+}
+// block table for `entries` keys at load <= 0.5; rebuilt from the live rows when it grows
+int ensure_btab(mmg_map* m, u64 entries, cudaStream_t st)
+{
+    TreesState* s   = m->trees;
+    const u64   cap = pow2_for(entries, 1024);
+    if (cap <= s->bcap) return MMG_OK;
+    MMG_CUDA(cudaStreamSynchronize(st));
+    Entry* t  = nullptr;
+    int    rc = new_table(&t, cap);
+    if (rc) return rc;
+    if (s->dev.btab) cudaFree(s->dev.btab);
+    s->dev.btab = t, s->dev.bmask = cap - 1, s->bcap = cap;
+    if (s->brow_hi) MMG_LAUNCH(k_trees_rebuild_btab, (s->brow_hi + 255) / 256, 256, 0, st, s->dev, s->brow_hi);
+    return MMG_OK;
+}
+// cell table: grow (or rebuild in place after an eviction) by rehashing the old table
+int rehash_ctab(mmg_map* m, u64 cap, cudaStream_t st)
+{
+    TreesState* s = m->trees;
+    MMG_CUDA(cudaStreamSynchronize(st));
+    Entry*    old    = s->dev.ctab;
+    const u64 oldcap = s->ccap;
+    Entry*    t      = nullptr;
+    int       rc     = new_table(&t, cap);
+    if (rc) return rc;
+    s->dev.ctab = t, s->dev.cmask = cap - 1, s->ccap = cap;
+    if (old)
+    {
+        MMG_LAUNCH(k_trees_rehash_ctab, (unsigned)((oldcap + 255) / 256), 256, 0, st, s->dev, (const Entry*)old, oldcap);
+        MMG_CUDA(cudaStreamSynchronize(st));
+        cudaFree(old);
+    }
+    return MMG_OK;
+}
+int ensure_ctab(mmg_map* m, u64 entries, cudaStream_t st)
+{
+    const u64 cap = pow2_for(entries, 4096);
+    return cap <= m->trees->ccap ? MMG_OK : rehash_ctab(m, cap, st);
+}
+void set_grid(mmg_map* m)
+{  // setGridProperties, SparseTreesPointCloud.cpp:176-189
+    TreesState* s = m->trees;
+    s->dev.g      = m->prm.voxel_size;
+    s->dev.ginv   = 1.0f / s->dev.g;
+    s->dev.ghalf  = 0.5f * s->dev.g;
+    s->dev.bbox   = m->dev.ctr->bbox;
+}
+}  // namespace
+
+int trees_create(mmg_map* m)
+{
+    TreesState* s = new TreesState();
+    m->trees      = s;
+    MMG_CUDA(cudaMalloc(&s->dev.ctr, sizeof(TreesCounters)));
+    MMG_CUDA(cudaMemset(s->dev.ctr, 0, sizeof(TreesCounters)));
+    MMG_CUDA(cudaMallocHost(&s->h_ctr, sizeof(TreesCounters)));
+    set_grid(m);
+    int rc = ensure_btab(m, 256, 0);
+    if (!rc) rc = ensure_ctab(m, 1024, 0);
+    return rc;
+}
+int trees_destroy(mmg_map* m)
+{
+    TreesState* s = m->trees;
+    if (!s) return MMG_OK;
+    cudaFree(s->dev.btab), cudaFree(s->dev.bkey), cudaFree(s->dev.bcnt), cudaFree(s->dev.l1), cudaFree(s->dev.l0), cudaFree(s->dev.bfree);
+    cudaFree(s->dev.ctab), cudaFree(s->dev.cpts), cudaFree(s->dev.cnext), cudaFree(s->dev.cfree), cudaFree(s->dev.ctr);
+    if (s->h_ctr) cudaFreeHost(s->h_ctr);
+    delete s;
+    m->trees = nullptr;
+    return MMG_OK;
+}
+int trees_clear(mmg_map* m)
+{
+    TreesState* s = m->trees;
+    MMG_CUDA(cudaMemset(s->dev.btab, 0xFF, s->bcap * sizeof(Entry)));
+    MMG_CUDA(cudaMemset(s->dev.ctab, 0xFF, s->ccap * sizeof(Entry)));
+    if (s->brows)
+    {
+        MMG_CUDA(cudaMemset(s->dev.bkey, 0xFF, s->brows * sizeof(u64)));
+        MMG_CUDA(cudaMemset(s->dev.bcnt, 0, s->brows * sizeof(u32)));
+        MMG_CUDA(cudaMemset(s->dev.l1, 0, s->brows * 16 * sizeof(u32)));
+        MMG_CUDA(cudaMemset(s->dev.l0, 0, s->brows * 1024 * sizeof(u32)));
+    }
+    MMG_CUDA(cudaMemset(s->dev.ctr, 0, sizeof(TreesCounters)));
+    s->brow_hi = s->bfree_n = s->crow_hi = s->cfree_n = s->ncells = 0;
+    s->npoints = 0;
+    return MMG_OK;
+}
+int trees_set_grid(mmg_map* m)
+{
+    set_grid(m);
+    return MMG_OK;
+}
+int trees_clone(const mmg_map* src, mmg_map* dst)
+{
+    const TreesState* a = src->trees;
+    TreesState*       b = dst->trees;
+    int               rc;
+    if (a->bcap != b->bcap)
+    {
+        cudaFree(b->dev.btab);
+        b->dev.btab = nullptr;
+        if ((rc = new_table(&b->dev.btab, a->bcap))) return rc;
+        b->bcap = a->bcap, b->dev.bmask = a->bcap - 1;
+    }
+    if (a->ccap != b->ccap)
+    {
+        cudaFree(b->dev.ctab);
+        b->dev.ctab = nullptr;
+        if ((rc = new_table(&b->dev.ctab, a->ccap))) return rc;
+        b->ccap = a->ccap, b->dev.cmask = a->ccap - 1;
+    }
+    if ((rc = ensure_block_rows(dst, a->brows, 0)) || (rc = ensure_chain_rows(dst, a->crows, 0))) return rc;
+    const cudaMemcpyKind k = cudaMemcpyDeviceToDevice;
+    cudaMemcpy(b->dev.btab, a->dev.btab, a->bcap * sizeof(Entry), k);
+    cudaMemcpy(b->dev.ctab, a->dev.ctab, a->ccap * sizeof(Entry), k);
+    if (a->brows)
+    {
+        cudaMemcpy(b->dev.bkey, a->dev.bkey, a->brows * sizeof(u64), k);
+        cudaMemcpy(b->dev.bcnt, a->dev.bcnt, a->brows * sizeof(u32), k);
+        cudaMemcpy(b->dev.l1, a->dev.l1, a->brows * 16 * sizeof(u32), k);
+        cudaMemcpy(b->dev.l0, a->dev.l0, a->brows * 1024 * sizeof(u32), k);
+        cudaMemcpy(b->dev.bfree, a->dev.bfree, a->brows * sizeof(u32), k);
+    }
+    if (a->crows)
+    {
+        cudaMemcpy(b->dev.cpts, a->dev.cpts, a->crows * TR_ROW * sizeof(float4), k);
+        cudaMemcpy(b->dev.cnext, a->dev.cnext, a->crows * sizeof(u32), k);
+        cudaMemcpy(b->dev.cfree, a->dev.cfree, a->crows * sizeof(u32), k);
+    }
+    cudaMemcpy(b->dev.ctr, a->dev.ctr, sizeof(TreesCounters), k);
+    cudaMemcpy(dst->dev.ctr, src->dev.ctr, sizeof(Counters), k);
+    b->brow_hi = a->brow_hi, b->bfree_n = a->bfree_n, b->crow_hi = a->crow_hi, b->cfree_n = a->cfree_n, b->ncells = a->ncells, b->npoints = a->npoints;
+    MMG_CUDA(cudaGetLastError());
+    return MMG_OK;
+}
+
+// ------------------------------------------------------------------ insert
+int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, int has_robot_pose, int mem,
+                 cudaStream_t st)
+{
+    TreesState*       s = m->trees;
+    const mmg_params& P = m->prm;
+    int               rc;
+    // eraseGridsFartherThan(:961-1000); the option is held in a float member (:893)
+    if (has_robot_pose && pose12 && P.remove_voxels_farther_than > 0 && s->brow_hi > s->bfree_n)
+    {
+        const float dist = (float)P.remove_voxels_farther_than;
+        const float t[3] = {(float)pose12[9], (float)pose12[10], (float)pose12[11]};
+        const int   c[3] = {(int)((t[0] + s->dev.ghalf) * s->dev.ginv), (int)((t[1] + s->dev.ghalf) * s->dev.ginv), (int)((t[2] + s->dev.ghalf) * s->dev.ginv)};
+        const int   d    = (int)std::ceil(dist * s->dev.ginv);
+        const u32   before = s->bfree_n;
+        MMG_LAUNCH(k_trees_evict, (unsigned)(((u64)s->brow_hi * 32 + 255) / 256), 256, 0, st, s->dev, s->brow_hi, c[0], c[1], c[2], d);
+        if ((rc = read_ctr(m, st))) return rc;
+        if (s->bfree_n != before)
+        {
+            MMG_CUDA(cudaMemsetAsync(s->dev.btab, 0xFF, s->bcap * sizeof(Entry), st));
+            MMG_LAUNCH(k_trees_rebuild_btab, (s->brow_hi + 255) / 256, 256, 0, st, s->dev, s->brow_hi);
+            if ((rc = rehash_ctab(m, s->ccap, st))) return rc;  // drops the cells of the erased blocks
+            if ((rc = read_ctr(m, st))) return rc;
+        }
+    }
+    if (n == 0) return MMG_OK;
+    if (n >= (1ull << 31))
+    {
+        set_error("insert batch too large (%zu points; limit 2^31-1)", n);
+        return MMG_ERR_INVALID_ARG;
+    }
+    const float *dx, *dy, *dz;
+    if ((rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz))) return rc;
+    const u32      N  = (u32)n;
+    const unsigned gN = (N + 255) / 256;
+    float4*        gp = (float4*)m->scratch_get(S_GP, n * sizeof(float4));
+    float4*        acc = (float4*)m->scratch_get(S_TREES0, n * sizeof(float4));
+    // u32 scratch: d2 | flag | pos (+ scan scratch) | bid | cslot | seg
+    const size_t w1   = 6 * n + scan_scratch_elems(n) + 16;
+    u32*         wrk  = (u32*)m->scratch_get(S_TREES1, w1 * sizeof(u32));
+    u32*         sbuf = (u32*)m->scratch_get(S_SORT, sort_scratch_words(n) * sizeof(u32));
+    if (!gp || !acc || !wrk || !sbuf) return MMG_ERR_OUT_OF_MEM;
+    float* d2   = (float*)wrk;
+    u32 *  flag = wrk + n, *pos = wrk + 2 * n, *bid = wrk + 3 * n + 1, *cslot = wrk + 4 * n + 1, *seg = wrk + 5 * n + 1, *bsum = wrk + 6 * n + 2;
+    const SortScratch ss = sort_scratch_at(sbuf, n);
+
+    // phase 1: compose, nearest neighbour in the pre-batch map, clearance test
+    const PoseD T = make_pose(pose12);
+    MMG_LAUNCH(k_trees_compose, gN, 256, 0, st, dx, dy, dz, N, T, gp);
+    const float*   gq = (const float*)gp;
+    const unsigned nb = persistent_blocks(m, n, 8, 8);
+    MMG_LAUNCH(k_trees_nn1, nb, 256, 0, st, s->dev, gq, gq + 1, gq + 2, N, 4u, T, 0, -1.0f, (uint8_t*)nullptr, (float*)nullptr, d2, (u64*)nullptr);
+    const float thr = P.minimum_points_clearance * P.minimum_points_clearance;
+    MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->oob, 0, sizeof(u32), st));
+    MMG_LAUNCH(k_trees_flags, gN, 256, 0, st, s->dev, gp, d2, N, thr, flag);
+    exclusive_scan<u32, u32>(flag, pos, n, pos + n, bsum, st);
+    u32 nacc = 0;
+    MMG_CUDA(cudaMemcpyAsync(&nacc, pos + n, sizeof(u32), cudaMemcpyDeviceToHost, st));
+    if ((rc = read_ctr(m, st))) return rc;  // synchronises; also fetches the out-of-range count
+    if (nacc)
+    {
+        // phase 2a: blocks
+        if ((rc = ensure_btab(m, (u64)(s->brow_hi - s->bfree_n) + nacc, st))) return rc;
+        MMG_LAUNCH(k_trees_locate, gN, 256, 0, st, s->dev, gp, flag, pos, N, acc, bid);
+        if ((rc = read_ctr(m, st))) return rc;
+        if ((rc = ensure_block_rows(m, s->brow_hi, st))) return rc;
+        u32* segse = (u32*)m->scratch_get(S_TREES2, 2 * (size_t)s->brows * sizeof(u32));
+        if (!segse) return MMG_ERR_OUT_OF_MEM;
+        u32 *         sbid, *sidx;
+        const unsigned gA = (nacc + 255) / 256;
+        radix_sort_index(bid, nacc, s->brow_hi, ss, &sbid, &sidx, st);
+        MMG_LAUNCH(k_trees_block_segs, gA, 256, 0, st, sbid, nacc, segse, segse + s->brows);
+        // phase 2b: block-local indices, cells
+        if ((rc = ensure_ctab(m, (u64)s->ncells + nacc, st))) return rc;
+        MMG_LAUNCH(k_trees_assign, gA, 256, 0, st, s->dev, sbid, sidx, nacc, segse, acc, cslot);
+        MMG_LAUNCH(k_trees_commit_blocks, gA, 256, 0, st, s->dev, sbid, sidx, nacc, segse, segse + s->brows, acc);
+        u32 *sslot, *sidx2;
+        radix_sort_index(cslot, nacc, (u32)(s->ccap - 1), ss, &sslot, &sidx2, st);
+        MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->nseg, 0, 2 * sizeof(u32), st));  // nseg, need_rows
+        MMG_LAUNCH(k_trees_cell_heads, gA, 256, 0, st, s->dev, sslot, nacc, seg);
+        MMG_LAUNCH(k_trees_cell_need, gA, 256, 0, st, s->dev, sslot, nacc, seg);
+        if ((rc = read_ctr(m, st))) return rc;
+        if ((rc = ensure_chain_rows(m, (u64)s->crow_hi + s->h_ctr->need_rows, st))) return rc;
+        const unsigned ab = persistent_blocks(m, s->h_ctr->nseg, 8, 8);
+        MMG_LAUNCH(k_trees_append, ab, 256, 0, st, s->dev, sslot, sidx2, nacc, seg, acc);
+        if ((rc = read_ctr(m, st))) return rc;
+    }
+    MMG_CUDA(cudaGetLastError());
+    if (s->h_ctr->oob)
+    {
+        set_error("%u of %zu points have a block index outside +-2^20 and were skipped", s->h_ctr->oob, n);
+        return MMG_ERR_OUT_OF_RANGE;
+    }
+    return MMG_OK;
+}
+
+// ----------------------------------------------------------------- queries
+int trees_nn_single(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, size_t stride, const double* pose12,
+                    uint8_t* ofound, float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st)
+{
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (n == 0) return MMG_OK;
+    const size_t nq = (n + stride - 1) / stride;
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    uint8_t* df = ofound;
+    float *  dxyz = oxyz, *dd2 = od2;
+    u64*     did = (u64*)oid;
+    if (mem == MMG_MEM_HOST)
+    {
+        char* ob = (char*)m->scratch_get(S_OUT, nq * 32);
+        if (!ob) return MMG_ERR_OUT_OF_MEM;
+        did = (u64*)ob, dxyz = (float*)(ob + nq * 8), dd2 = (float*)(ob + nq * 20), df = (uint8_t*)(ob + nq * 24);
+    }
+    const PoseD    T  = make_pose(pose12);
+    const unsigned nb = persistent_blocks(m, nq, 8, 8);
+    MMG_LAUNCH(k_trees_nn1, nb, 256, 0, st, m->trees->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, 0.0f, df, dxyz, dd2, did);
+    MMG_CUDA(cudaGetLastError());
+    if (mem == MMG_MEM_HOST)
+    {
+        MMG_CUDA(cudaMemcpyAsync(oid, did, nq * 8, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(oxyz, dxyz, nq * 12, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(od2, dd2, nq * 4, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(ofound, df, nq, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaStreamSynchronize(st));
+    }
+    return MMG_OK;
+}
+
+int trees_nn_multi(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, size_t k, uint32_t* ocount,
+                   float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st)
+{
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (n == 0) return MMG_OK;
+    if (k > 32)
+    {
+        set_error("SparseTrees nn_multiple_search: k <= 32 supported on the device (got %zu)", k);
+        return MMG_ERR_UNSUPPORTED;
+    }
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    u32*   dc = ocount;
+    float *dxyz = oxyz, *dd2 = od2;
+    u64*   did = (u64*)oid;
+    if (mem == MMG_MEM_HOST)
+    {
+        char* ob = (char*)m->scratch_get(S_OUT, n * k * 24 + n * 4 + 64);
+        if (!ob) return MMG_ERR_OUT_OF_MEM;
+        did = (u64*)ob, dxyz = (float*)(ob + n * k * 8), dd2 = (float*)(ob + n * k * 20), dc = (u32*)(ob + n * k * 24);
+    }
+    const PoseD    T  = make_pose(pose12);
+    const unsigned nb = persistent_blocks(m, n, 8, 8);
+    MMG_LAUNCH(k_trees_knn, nb, 256, 0, st, m->trees->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, (u32)k, dc, dxyz, dd2, did);
+    MMG_CUDA(cudaGetLastError());
+    if (mem == MMG_MEM_HOST)
+    {
+        MMG_CUDA(cudaMemcpyAsync(oid, did, n * k * 8, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(oxyz, dxyz, n * k * 12, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(od2, dd2, n * k * 4, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(ocount, dc, n * 4, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaStreamSynchronize(st));
+    }
+    return MMG_OK;
+}
+
+int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float r2, size_t maxp_, uint64_t* ooff,
+                 uint64_t* ototal, int mem, cudaStream_t st)
+{
+    TreesState*  s = m->trees;
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    const float r    = r2 > 0 ? std::sqrt(r2) : 0.f;
+    const u32   maxp = (u32)std::min<size_t>(maxp_, 0xFFFFFFFFu);
+    // blocks per axis that [q - r, q + r] can touch, +1 for the double-width index 0
+    const u64 per_axis = (u64)std::floor(2.0 * r / s->dev.g) + 2;
+    const u64 nbq      = per_axis * per_axis * per_axis;
+    if (nbq * (u64)n >= (1ull << 31))
+    {
+        set_error("nn_radius_search: radius spans %llu blocks per query x %zu queries; split the batch", (unsigned long long)nbq, n);
+        return MMG_ERR_INVALID_ARG;
+    }
+    const size_t nseg = (size_t)nbq * n;
+    u64*         qoff = (u64*)m->scratch_get(S_ROFF, (n + 2 + scan_scratch_elems(n)) * sizeof(u64));
+    if (!qoff) return MMG_ERR_OUT_OF_MEM;
+    u64 total = 0;
+    MMG_CUDA(cudaMemsetAsync(qoff, 0, (n + 1) * sizeof(u64), st));
+    if (n)
+    {
+        u32* counts = (u32*)m->scratch_get(S_RCNT, (nseg + 1) * sizeof(u32));
+        u64* segoff = (u64*)m->scratch_get(S_TREES3, (nseg + 2 + scan_scratch_elems(nseg)) * sizeof(u64));
+        if (!counts || !segoff) return MMG_ERR_OUT_OF_MEM;
+        const PoseD    T  = make_pose(pose12);
+        const unsigned nb = persistent_blocks(m, n, 8, 8);
+        MMG_LAUNCH((k_trees_radius<0>), nb, 256, 0, st, s->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, r2, r, (u32)nbq, counts, (const u64*)nullptr,
+                   (float*)nullptr, (float*)nullptr, (u32*)nullptr, (u32*)nullptr);
+        exclusive_scan<u32, u64>(counts, segoff, nseg, segoff + nseg, segoff + nseg + 1, st);
+        u64 H = 0;
+        MMG_CUDA(cudaMemcpyAsync(&H, segoff + nseg, sizeof(u64), cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaStreamSynchronize(st));
+        if (H >= (1ull << 31))
+        {
+            set_error("nn_radius_search batch produced %llu hits (limit 2^31-1): split the batch", (unsigned long long)H);
+            return MMG_ERR_INVALID_ARG;
+        }
+        if (H)
+        {
+            // source hits: id (u64) | xyz | d2, plus idx / seg / qkey (u32 each)
+            char* hb   = (char*)m->scratch_get(S_RHITS, H * 24);
+            u32*  aux  = (u32*)m->scratch_get(S_QID, 4 * H * sizeof(u32));
+            u32*  sbuf = (u32*)m->scratch_get(S_HSORT, sort_scratch_words(H) * sizeof(u32));
+            u32*  work = (u32*)m->scratch_get(S_HWORK, hits_work_words(H, n) * sizeof(u32));
+            if (!hb || !aux || !sbuf || !work) return MMG_ERR_OUT_OF_MEM;
+            u64*              sid  = (u64*)hb;
+            float*            sxyz = (float*)(hb + H * 8);
+            float*            sd2  = (float*)(hb + H * 20);
+            u32 *             hidx = aux, *hseg = aux + H, *qkey = aux + 2 * H, *key = aux + 3 * H;
+            const SortScratch ss   = sort_scratch_at(sbuf, H);
+            const unsigned    gH   = (unsigned)((H + 255) / 256);
+            MMG_LAUNCH((k_trees_radius<1>), nb, 256, 0, st, s->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, r2, r, (u32)nbq, counts, segoff, sxyz, sd2, hidx,
+                       hseg);
+            MMG_LAUNCH(k_trees_idx_to_id, gH, 256, 0, st, hidx, (u32)H, sid);
+            // per block: ascending (d2, index), cut at maxPoints -> order (segment, d2, index)
+            u32 *sk, *p1, *p2, *p3;
+            MMG_LAUNCH(k_hits_gather_u32, gH, 256, 0, st, hidx, (const u32*)nullptr, (u32)H, key);
+            radix_sort_pairs(key, nullptr, H, (u32)std::min<u64>(s->npoints, 0xFFFFFFFFull), ss, &sk, &p1, st);
+            MMG_LAUNCH(k_hits_gather_d2, gH, 256, 0, st, sd2, (const u32*)p1, (u32)H, key);
+            radix_sort_pairs(key, p1, H, 0xFFFFFFFFu, ss, &sk, &p2, st);
+            MMG_LAUNCH(k_hits_gather_u32, gH, 256, 0, st, hseg, (const u32*)p2, (u32)H, key);
+            radix_sort_pairs(key, p2, H, (u32)(nseg - 1), ss, &sk, &p3, st);
+            MMG_LAUNCH(k_trees_trunc_keys, gH, 256, 0, st, sk, p3, segoff, (u32)H, (u32)nbq, maxp, (u32)n, qkey);
+            // p3 lives in the sort scratch that hits_map_semantics is about to reuse: move it out
+            MMG_CUDA(cudaMemcpyAsync(hseg, p3, H * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+            // merge through the std::map<float,...>: equal d2 collapse, last block / highest index wins; not re-truncated
+            if ((rc = hits_map_semantics(m, (u32)n, (u32)H, qkey, hseg, ss, work, sxyz, sd2, sid, 0u, qoff, &total, st))) return rc;
+        }
+        else
+            m->rad_total = 0;
+    }
+    else
+        m->rad_total = 0;
+    MMG_CUDA(cudaGetLastError());
+    MMG_CUDA(cudaMemcpyAsync(ooff, qoff, (n + 1) * sizeof(u64), mem == MMG_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    if (ototal) *ototal = total;
+    return MMG_OK;
+}
+
+// ------------------------------------------------------------------- misc
+int trees_is_empty(const mmg_map* m, int* out)
+{
+    *out = (m->trees->brow_hi - m->trees->bfree_n) == 0;
+    return MMG_OK;
+}
+int trees_num_blocks(const mmg_map* m, uint64_t* out)
+{
+    *out = m->trees->brow_hi - m->trees->bfree_n;
+    return MMG_OK;
+}
+int trees_num_points(const mmg_map* m, uint64_t* out)
+{
+    *out = m->trees->npoints;
+    return MMG_OK;
+}
+// live flags + ranks of the block rows; returns the largest block (the export row stride)
+static int block_ranks(mmg_map* m, u32** rank_out, u32* maxcnt, cudaStream_t st)
+{
+    TreesState* s  = m->trees;
+    const u32   nr = s->brow_hi;
+    u32*        lr = (u32*)m->scratch_get(S_SEG, (2 * (size_t)nr + 2 + scan_scratch_elems(nr)) * sizeof(u32));
+    if (!lr) return MMG_ERR_OUT_OF_MEM;
+    u32* rank = lr + nr + 1;
+    MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->maxcnt, 0, sizeof(u32), st));
+    MMG_LAUNCH(k_trees_live, (nr + 255) / 256, 256, 0, st, s->dev, nr, lr);
+    exclusive_scan<u32, u32>(lr, rank, nr, (u32*)nullptr, rank + nr + 1, st);
+    int rc = read_ctr(m, st);
+    if (rc) return rc;
+    *rank_out = rank;
+    *maxcnt   = s->h_ctr->maxcnt;
+    return MMG_OK;
+}
+int trees_row_capacity(const mmg_map* cm, uint32_t* out)
+{
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    *out       = 0;
+    if (m->trees->brow_hi == m->trees->bfree_n) return MMG_OK;
+    u32* rank;
+    return block_ranks(m, &rank, out, 0);
+}
+int trees_export(const mmg_map* cm, int32_t* keys, uint32_t* counts, float* points, int mem, cudaStream_t st)
+{
+    mmg_map*    m = const_cast<mmg_map*>(cm);
+    TreesState* s = m->trees;
+    const u64   V = s->brow_hi - s->bfree_n;
+    if (!V) return MMG_OK;
+    u32 *rank, cap = 0;
+    int  rc = block_ranks(m, &rank, &cap, st);
+    if (rc) return rc;
+    int32_t* dk = keys;
+    u32*     dc = counts;
+    float*   dp = points;
+    if (mem == MMG_MEM_HOST)
+    {
+        char* ob = (char*)m->scratch_get(S_OUT, V * 16 + (points ? V * cap * 12 : 0) + 64);
+        if (!ob) return MMG_ERR_OUT_OF_MEM;
+        dk = (int32_t*)ob, dc = (u32*)(ob + V * 12), dp = points ? (float*)(ob + V * 16) : nullptr;
+    }
+    MMG_LAUNCH(k_trees_export_blocks, (s->brow_hi + 255) / 256, 256, 0, st, s->dev, s->brow_hi, rank, dk, dc);
+    if (dp)
+    {
+        MMG_CUDA(cudaMemsetAsync(dp, 0, V * cap * 12, st));
+        MMG_LAUNCH(k_trees_export_points, (unsigned)((s->ccap * 32 + 255) / 256), 256, 0, st, s->dev, s->ccap, rank, cap, dp, (u32*)nullptr);
+    }
+    MMG_CUDA(cudaGetLastError());
+    if (mem == MMG_MEM_HOST)
+    {
+        if (keys) MMG_CUDA(cudaMemcpyAsync(keys, dk, V * 12, cudaMemcpyDeviceToHost, st));
+        if (counts) MMG_CUDA(cudaMemcpyAsync(counts, dc, V * 4, cudaMemcpyDeviceToHost, st));
+        if (points) MMG_CUDA(cudaMemcpyAsync(points, dp, V * cap * 12, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaStreamSynchronize(st));
+    }
+    return MMG_OK;
+}
+int trees_bbox_from_points(mmg_map* m)
+{  // boundingBox() without a cached value: over all points (SparseTreesPointCloud.cpp:715-741)
+    TreesState* s = m->trees;
+    MMG_LAUNCH(k_trees_export_points, (unsigned)((s->ccap * 32 + 255) / 256), 256, 0, 0, s->dev, s->ccap, (const u32*)nullptr, 0u, (float*)nullptr,
+               m->dev.ctr->bbox);
+    MMG_CUDA(cudaGetLastError());
+    return MMG_OK;
+}
+int trees_table_stats(mmg_map* m, mmg_table_stats* out)
+{
+    TreesState* s    = m->trees;
+    out->capacity    = s->ccap;
+    out->live_voxels = s->brow_hi - s->bfree_n;
+    out->points      = s->npoints;
+    out->load_factor = s->ccap ? (double)s->ncells / (double)s->ccap : 0;
+    out->hbm_bytes   = s->bcap * sizeof(Entry) + s->ccap * sizeof(Entry) + s->brows * (8 + 4 + 64 + 4096 + 4) + s->crows * (TR_ROW * 16 + 8);
+    return MMG_OK;
+}
+
+namespace mmg
+{
+// replicate from `root`: sizes first (host header already exchanged by the caller), then the flat buffers
+int trees_bcast(mmg_map* m, int root, int rank, void* comm, cudaStream_t st, u64 npoints, u64 nblocks,
+                int (*bcast)(void*, void*, size_t, int, cudaStream_t))
+{
+    TreesState* s = m->trees;
+    struct Sizes
+    {
+        u64 bcap, brows, ccap, crows;
+    } h{s->bcap, s->brow_hi, s->ccap, s->crow_hi};
+    Sizes* dh = (Sizes*)m->scratch_get(S_OUT, sizeof(Sizes) + 64);
+    if (!dh) return MMG_ERR_OUT_OF_MEM;
+    if (rank == root) MMG_CUDA(cudaMemcpyAsync(dh, &h, sizeof(h), cudaMemcpyHostToDevice, st));
+    int rc = bcast(comm, dh, sizeof(h), root, st);
+    if (rc) return rc;
+    MMG_CUDA(cudaMemcpyAsync(&h, dh, sizeof(h), cudaMemcpyDeviceToHost, st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    if (rank != root)
+    {
+        if (s->bcap != h.bcap)
+        {
+            cudaFree(s->dev.btab);
+            s->dev.btab = nullptr;
+            if ((rc = new_table(&s->dev.btab, h.bcap))) return rc;
+            s->bcap = h.bcap, s->dev.bmask = h.bcap - 1;
+        }
+        if (s->ccap != h.ccap)
+        {
+            cudaFree(s->dev.ctab);
+            s->dev.ctab = nullptr;
+            if ((rc = new_table(&s->dev.ctab, h.ccap))) return rc;
+            s->ccap = h.ccap, s->dev.cmask = h.ccap - 1;
+        }
+        if ((rc = ensure_block_rows(m, h.brows, st)) || (rc = ensure_chain_rows(m, h.crows, st))) return rc;
+    }
+    const TreesDev& d = s->dev;
+    if ((rc = bcast(comm, d.btab, h.bcap * sizeof(Entry), root, st))) return rc;
+    if ((rc = bcast(comm, d.ctab, h.ccap * sizeof(Entry), root, st))) return rc;
+    if ((rc = bcast(comm, d.bkey, h.brows * sizeof(u64), root, st))) return rc;
+    if ((rc = bcast(comm, d.bcnt, h.brows * sizeof(u32), root, st))) return rc;
+    if ((rc = bcast(comm, d.l1, h.brows * 16 * sizeof(u32), root, st))) return rc;
+    if ((rc = bcast(comm, d.l0, h.brows * 1024 * sizeof(u32), root, st))) return rc;
+    if ((rc = bcast(comm, d.bfree, h.brows * sizeof(u32), root, st))) return rc;
+    if ((rc = bcast(comm, d.cpts, h.crows * TR_ROW * sizeof(float4), root, st))) return rc;
+    if ((rc = bcast(comm, d.cnext, h.crows * sizeof(u32), root, st))) return rc;
+    if ((rc = bcast(comm, d.cfree, h.crows * sizeof(u32), root, st))) return rc;
+    if ((rc = bcast(comm, d.ctr, sizeof(TreesCounters), root, st))) return rc;
+    if ((rc = bcast(comm, m->dev.ctr, sizeof(Counters), root, st))) return rc;
+    (void)npoints, (void)nblocks;
+    return read_ctr(m, st);
+}
+}  // namespace mmg

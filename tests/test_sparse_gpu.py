@@ -1,0 +1,165 @@
+"""GPU parity of the SparseVoxelPointCloud and SparseTreesPointCloud paths against the CPU oracle,
+through the C ABI. Bit-exact: block / voxel sets, ordered point lists, ids, points, d2, CSR offsets."""
+import numpy as np
+import pytest
+
+from conftest import GpuAdapter, bits, compose_host
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(kind, size, **opts):
+    from oracle import mmo
+    return GpuAdapter(kind, size, **opts), mmo.OracleMap(kind, size, **opts)
+
+
+def _scan(sensor="tiny", s=0.0, scan_id=0):
+    from mola_b200 import synth
+    return synth.lidar_scan(sensor, s=s, scan_id=scan_id)
+
+
+def _same_export(g, o):
+    gk, gc, gp = g.export()
+    ok, oc, op = o.export()
+    assert np.array_equal(gk, ok) and np.array_equal(gc, oc)
+    assert gp.shape == op.shape and np.array_equal(bits(gp), bits(op))
+
+
+def _same_radius(g, o, q, r, mp):
+    a = g.nn_radius(*q, np.float32(r * r), mp)
+    b = o.nn_radius(*q, np.float32(r * r), mp)
+    assert np.array_equal(a[0], b[0]), f"offsets differ r={r} maxp={mp}"
+    assert np.array_equal(a[3], b[3])
+    assert np.array_equal(bits(a[2]), bits(b[2])) and np.array_equal(bits(a[1]), bits(b[1]))
+    return int(b[0][-1])
+
+
+@pytest.mark.parametrize("opts", [dict(), dict(max_points_per_voxel=3), dict(match_mean=1), dict(match_mean=1, max_points_per_voxel=20)])
+def test_sparse_voxel_insert_radius(built, opts):
+    g, o = _pair(1, 0.2, **opts)
+    for k in range(3):
+        sc = _scan("tiny", s=1.0 * k, scan_id=k)
+        g.insert(*sc)
+        o.insert(*sc)
+        _same_export(g, o)
+    assert np.array_equal(np.concatenate(g.bbox()), np.concatenate(o.bbox()))
+    gm, gcov = g.voxel_stats()
+    om, ocov = o.voxel_stats()
+    assert np.array_equal(bits(gm), bits(om))
+    assert np.allclose(gcov, ocov, rtol=1e-5, atol=1e-9)
+    q = compose_host(sc[3], sc[0] + np.float32(0.03), sc[1], sc[2])
+    hits = 0
+    for r, mp in ((0.15, 0), (0.45, 0), (0.45, 3), (0.8, 16), (0.3, 1)):
+        hits += _same_radius(g, o, q, r, mp)
+    assert hits > 0
+
+
+def test_sparse_voxel_c3_knn_extension(built):
+    """BASELINE config 3 (extension): k=8 stencil k-NN == brute force over the 27-cell stencil."""
+    from mola_b200 import MapError, SparseVoxelPointCloud
+    from oracle import mmo
+    m = SparseVoxelPointCloud(0.2)
+    o = mmo.OracleMap(1, 0.2)
+    xs, ys, zs, pose = _scan("hdl64")
+    m.insertPointCloud(xs, ys, zs, pose)
+    o.insert(xs, ys, zs, pose)
+    q = [c[::13].copy() for c in compose_host(pose, xs + np.float32(0.02), ys, zs)]
+    with pytest.raises(MapError):
+        m.nn_multiple_search_batch(*q, 8)
+    m.enable_knn_extension = True
+    cnt, pts, d2, ids = m.nn_multiple_search_batch(*q, 8)
+    # brute force over the exported map, restricted to the 27-cell stencil of round-based indices
+    keys, counts, P = o.export()
+    lut = {tuple(k): i for i, k in enumerate(keys)}
+    inv = np.float32(1.0) / np.float32(0.2)
+    for j in range(0, q[0].size, 97):
+        c = [int(np.rint(np.float32(q[a][j]) * inv)) for a in range(3)]
+        cand = []
+        for dx in (-1, 0, 1):
+            for dy in (-1, 0, 1):
+                for dz in (-1, 0, 1):
+                    i = lut.get((c[0] + dx, c[1] + dy, c[2] + dz))
+                    if i is None:
+                        continue
+                    for s in range(counts[i]):
+                        p = P[i, s]
+                        dd = [np.float32(p[a]) - np.float32(q[a][j]) for a in range(3)]
+                        cand.append((np.float32(np.float32(dd[0] * dd[0] + dd[1] * dd[1]) + dd[2] * dd[2]), len(cand)))
+        cand.sort()
+        k = min(8, len(cand))
+        assert cnt[j] == k
+        assert np.array_equal(d2[j, :k], np.array([c_[0] for c_ in cand[:k]], np.float32))
+
+
+@pytest.mark.parametrize("opts", [dict(), dict(minimum_points_clearance=0.5), dict(minimum_points_clearance=0.05, remove_voxels_farther_than=25.0)])
+def test_sparse_trees(built, opts):
+    g, o = _pair(2, 10.0, **opts)
+    for k in range(4):
+        sc = _scan("tiny", s=9.0 * k, scan_id=k)
+        g.insert(*sc)
+        o.insert(*sc)
+        _same_export(g, o)
+        assert g.num_points() == o.num_points()
+    assert np.array_equal(np.concatenate(g.bbox()), np.concatenate(o.bbox()))
+    q = compose_host(sc[3], sc[0] + np.float32(0.07), sc[1] - np.float32(0.03), sc[2])
+    a, b = g.nn_single(*q), o.nn_single(*q)
+    assert np.array_equal(a[0], b[0])
+    k = b[0] > 0
+    assert k.any()
+    assert np.array_equal(a[3][k], b[3][k]) and np.array_equal(bits(a[2][k]), bits(b[2][k])) and np.array_equal(bits(a[1][k]), bits(b[1][k]))
+    for kk in (1, 3, 8, 32):
+        ma, mb = g.nn_multi(*q, kk), o.nn_multi(*q, kk)
+        assert np.array_equal(ma[0], mb[0])
+        msk = np.arange(kk)[None, :] < mb[0][:, None]
+        assert np.array_equal(ma[3][msk], mb[3][msk]) and np.array_equal(bits(ma[2][msk]), bits(mb[2][msk]))
+        assert np.array_equal(bits(ma[1][msk]), bits(mb[1][msk]))
+    for r, mp in ((0.2, 0), (1.0, 0), (2.0, 0), (2.0, 4), (6.0, 2)):
+        _same_radius(g, o, q, r, mp)
+    la, lb = g.likelihood(*sc[:3], sc[3]), o.likelihood(*sc[:3], sc[3])
+    assert abs(la - lb) <= 1e-12 * abs(lb)
+
+
+def test_sparse_trees_full_scan_far_queries(built):
+    """Exactness of the branch-and-bound search: 120k-pt scans, queries far from any stored point,
+    negative coordinates and the double-width block 0."""
+    g, o = _pair(2, 10.0, minimum_points_clearance=0.1)
+    for k in range(2):
+        sc = _scan("hdl64", s=7.0 * k, scan_id=k)
+        g.insert(*sc)
+        o.insert(*sc)
+    _same_export(g, o)
+    rng = np.random.default_rng(5)
+    n = 4000
+    q = [rng.uniform(-60, 60, n).astype(np.float32), rng.uniform(-25, 25, n).astype(np.float32), rng.uniform(-4, 12, n).astype(np.float32)]
+    a, b = g.nn_single(*q), o.nn_single(*q)
+    assert np.array_equal(a[0], b[0])
+    k = b[0] > 0
+    assert k.sum() > n // 4
+    assert np.array_equal(a[3][k], b[3][k]) and np.array_equal(bits(a[2][k]), bits(b[2][k]))
+    ma, mb = g.nn_multi(*q, 5), o.nn_multi(*q, 5)
+    assert np.array_equal(ma[0], mb[0])
+    msk = np.arange(5)[None, :] < mb[0][:, None]
+    assert np.array_equal(ma[3][msk], mb[3][msk]) and np.array_equal(bits(ma[2][msk]), bits(mb[2][msk]))
+    qs = [c[:300].copy() for c in q]
+    _same_radius(g, o, qs, 1.5, 0)
+    _same_radius(g, o, qs, 3.0, 7)
+
+
+def test_sparse_trees_clone_clear_empty(built):
+    from mola_b200 import SparseTreesPointCloud
+    m = SparseTreesPointCloud(10.0)
+    e = np.zeros(0, np.float32)
+    m.insertPointCloud(e, e, e)
+    assert m.isEmpty() and m.numVoxels() == 0 and m.numPoints() == 0
+    f, p, d, i = m.nn_single_search_batch(np.ones(3, np.float32), np.ones(3, np.float32), np.ones(3, np.float32))
+    assert not f.any()
+    off, p, d, i = m.nn_radius_search_batch(np.ones(3, np.float32), np.ones(3, np.float32), np.ones(3, np.float32), 4.0)
+    assert off[-1] == 0
+    xs, ys, zs, pose = _scan("tiny")
+    m.insertPointCloud(xs, ys, zs, pose)
+    c = m.clone()
+    n0 = m.numPoints()
+    m.clear()
+    assert m.isEmpty() and c.numPoints() == n0 and n0 > 0
+    k1, c1, p1, _ = c.exportVoxels()
+    assert int(c1.sum()) == n0
