@@ -283,16 +283,25 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
         o.id = (u64*)ob, o.xyz = (float*)(ob + nq * 8), o.d2 = (float*)(ob + nq * 20), o.found = (uint8_t*)(ob + nq * 24);
     }
     const PoseD    T  = make_pose(pose12);
-    static const bool simple = getenv("MMG_NN_SIMPLE") != nullptr;  // A/B switch: one warp per query, no grouping
-    if (simple)
+    // A/B switch for the profiles: MMG_NN_KERNEL = pruned (default) | grouped | simple
+    static const int variant = [] {
+        const char* e = getenv("MMG_NN_KERNEL");
+        return !e ? 0 : (!strcmp(e, "grouped") ? 1 : (!strcmp(e, "simple") ? 2 : 0));
+    }();
+    if (variant == 2)
     {
         const unsigned nb = persistent_blocks(m, nq, 8, 8);
         MMG_LAUNCH((k_nn_single<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, o);
     }
-    else
+    else if (variant == 1)
     {
         const unsigned nb = persistent_blocks(m, (nq + 31) / 32, 8, 8);
-        MMG_LAUNCH((k_nn_single_grouped<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, o);
+        MMG_LAUNCH((k_nn_single_grouped<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, m->prm.voxel_size, o);
+    }
+    else
+    {
+        const unsigned nb = (unsigned)std::min<size_t>((nq + 255) / 256, (size_t)m->num_sms * 64);
+        MMG_LAUNCH((k_nn_single_pruned<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, m->prm.voxel_size, o);
     }
     MMG_CUDA(cudaGetLastError());
     if (mem == MMG_MEM_HOST)

@@ -60,6 +60,12 @@ struct HashedTraits
         c = __float2int_rz(s);
         return true;
     }
+    // index range [lo, hi] (in voxel units) of the coordinates that truncate to c: index 0 spans (-1, 1)
+    __device__ static __forceinline__ void cell_span(int c, float& lo, float& hi)
+    {
+        lo = (float)(c > 0 ? c : c - 1);
+        hi = (float)(c < 0 ? c : c + 1);
+    }
 };
 struct SparseVoxelTraits
 {  // mola::SparseVoxelPointCloud: mrpt::round = lrint (ties to even), SparseVoxelPointCloud.h:108-115
@@ -71,7 +77,33 @@ struct SparseVoxelTraits
         c = __float2int_rn(s);
         return true;
     }
+    __device__ static __forceinline__ void cell_span(int c, float& lo, float& hi)
+    {
+        lo = (float)c - 0.5f;
+        hi = (float)c + 0.5f;
+    }
 };
+// Conservative lower bound of the squared distance between q and any point stored in voxel
+// (cx, cy, cz): the voxel's coordinate box is widened by a few ulps of its largest coordinate
+// (the index is computed from fl(x * fl(1/v))) and the result is scaled down, so a voxel is
+// only ever skipped when every point in it is strictly farther than the bound.
+template <class Tr>
+__device__ __forceinline__ float voxel_lower_bound(int cx, int cy, int cz, float vsize, float qx, float qy, float qz)
+{
+    const int   c[3] = {cx, cy, cz};
+    const float q[3] = {qx, qy, qz};
+    float       s    = 0.f;
+#pragma unroll
+    for (int a = 0; a < 3; a++)
+    {
+        float lo, hi;
+        Tr::cell_span(c[a], lo, hi);
+        const float eps = (fabsf((float)c[a]) + 2.0f) * vsize * 1e-6f;
+        const float d   = fmaxf(0.f, fmaxf(lo * vsize - eps - q[a], q[a] - (hi * vsize + eps)));
+        s += d * d;
+    }
+    return s * 0.9999f;
+}
 
 __device__ __host__ __forceinline__ bool index_in_range(int cx, int cy, int cz)
 {

@@ -15,15 +15,38 @@
 
 namespace mmg
 {
+// One pass over the stencil for G queries of the same voxel. `cells` = non-empty stencil cells
+// (bit b = lane b's cell), (bx, by, bz) = the group's voxel. The queries' own voxel goes first,
+// then only cells whose box can still hold a point at least as close as the current best of
+// one of the G queries (exact pruning: skipped cells hold strictly farther points only, so the
+// result, including the scan-order tie-break, is the one of the exhaustive walk).
 template <class Tr, int G>
-__device__ __forceinline__ void nn_group_pass(const VoxelMapDev& m, u32 cells, u32 vid, u32 cnt, int lane, const float (&gx)[G],
-                                              const float (&gy)[G], const float (&gz)[G], float (&bd)[G], u32 (&br)[G])
+__device__ __forceinline__ void nn_group_pass(const VoxelMapDev& m, u32 cells, u32 vid, u32 cnt, int lane, int bx, int by, int bz, float vsize,
+                                              const float (&gx)[G], const float (&gy)[G], const float (&gz)[G], float (&bd)[G], u32 (&br)[G],
+                                              u32 (&wb)[G])
 {
     constexpr int CAP = Tr::CAP;
-    while (cells)
+    float         lb[G];
     {
-        const int b = __ffs(cells) - 1;
-        cells &= cells - 1;
+        const int x = bx + lane / 9 - 1, y = by + (lane / 3) % 3 - 1, z = bz + lane % 3 - 1;
+#pragma unroll
+        for (int g = 0; g < G; g++) lb[g] = voxel_lower_bound<Tr>(x, y, z, vsize, gx[g], gy[g], gz[g]);
+    }
+#pragma unroll
+    for (int g = 0; g < G; g++) wb[g] = 0x7f800000u;
+    int b = (cells >> 13) & 1u ? 13 : -1;  // the queries' own voxel
+    for (;;)
+    {
+        if (b < 0)
+        {
+            bool can = false;
+#pragma unroll
+            for (int g = 0; g < G; g++) can |= !(lb[g] > __uint_as_float(wb[g]));
+            const u32 cand = __ballot_sync(MMG_FULL, can) & cells;
+            if (!cand) break;
+            b = __ffs(cand) - 1;
+        }
+        cells &= ~(1u << b);
         const u32 v = __shfl_sync(MMG_FULL, vid, b), c = __shfl_sync(MMG_FULL, cnt, b);
         if ((u32)lane < c)
         {
@@ -33,20 +56,23 @@ __device__ __forceinline__ void nn_group_pass(const VoxelMapDev& m, u32 cells, u
             for (int g = 0; g < G; g++)
             {
                 const float d = sqr_dist(t.x, t.y, t.z, gx[g], gy[g], gz[g]);
-                if (d < bd[g])
+                if (d < bd[g] || (d == bd[g] && rank < br[g]))
                 {
                     bd[g] = d;
                     br[g] = rank;
                 }
             }
         }
+#pragma unroll
+        for (int g = 0; g < G; g++) wb[g] = __reduce_min_sync(MMG_FULL, __float_as_uint(bd[g]));
+        b = -1;
     }
 }
 
 template <class Tr>
 __global__ void __launch_bounds__(256)
     k_nn_single_grouped(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride,
-                        PoseD pose, int use_pose, float inv, QueryOut out)
+                        PoseD pose, int use_pose, float inv, float vsize, QueryOut out)
 {
     constexpr int CAP     = Tr::CAP;
     constexpr int G       = 4;
@@ -115,22 +141,22 @@ __global__ void __launch_bounds__(256)
                     bd[g] = INF;
                     br[g] = 0xFFFFFFFFu;
                 }
+                u32 wb[G];
                 if (ng == 1)
                 {
                     float ax[1] = {gx[0]}, ay[1] = {gy[0]}, az[1] = {gz[0]}, ad[1] = {INF};
-                    u32   ar[1] = {0xFFFFFFFFu};
-                    nn_group_pass<Tr, 1>(m, cells, vid, cnt, lane, ax, ay, az, ad, ar);
-                    bd[0] = ad[0], br[0] = ar[0];
+                    u32   ar[1] = {0xFFFFFFFFu}, aw[1];
+                    nn_group_pass<Tr, 1>(m, cells, vid, cnt, lane, bx, by, bz, vsize, ax, ay, az, ad, ar, aw);
+                    bd[0] = ad[0], br[0] = ar[0], wb[0] = aw[0];
                 }
                 else
-                    nn_group_pass<Tr, G>(m, cells, vid, cnt, lane, gx, gy, gz, bd, br);
+                    nn_group_pass<Tr, G>(m, cells, vid, cnt, lane, bx, by, bz, vsize, gx, gy, gz, bd, br, wb);
 #pragma unroll
                 for (int g = 0; g < G; g++)
                 {
                     if (g >= ng) break;
-                    const u32 db   = __float_as_uint(bd[g]);
-                    const u32 dmin = __reduce_min_sync(MMG_FULL, db);
-                    const u32 rr   = __reduce_min_sync(MMG_FULL, db == dmin ? br[g] : 0xFFFFFFFFu);
+                    const u32 dmin = wb[g];
+                    const u32 rr   = __reduce_min_sync(MMG_FULL, __float_as_uint(bd[g]) == dmin ? br[g] : 0xFFFFFFFFu);
                     if (rr == 0xFFFFFFFFu) continue;  // cannot happen when cells != 0; kept for safety
                     const int    b = (int)(rr >> 5), slot = (int)(rr & 31);
                     const u32    v = __shfl_sync(MMG_FULL, vid, b);
@@ -152,6 +178,94 @@ __global__ void __launch_bounds__(256)
             out.id[q]    = rid;
             out.xyz[3 * (size_t)q] = rx, out.xyz[3 * (size_t)q + 1] = ry, out.xyz[3 * (size_t)q + 2] = rz;
         }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_nn_single_pruned: one THREAD per query, exact branch-and-bound over the 27-cell stencil.
+//
+// The reference visits all 27 cells; the answer is the minimum of (d2, scan rank), so any visiting
+// order and any pruning that only drops cells whose every point is strictly farther than the
+// current best give the same result. The query's own voxel goes first (it nearly always holds the
+// answer for ICP-style queries), then a neighbour is probed only if its box can still hold a
+// point at least as close. The box distance separates per axis, so it costs three table look-ups
+// in registers per cell. Consecutive LiDAR points fall into the same voxel, so the lanes of a warp
+// mostly read the same row and the loads coalesce into broadcasts; every lane does useful distance
+// evaluations (no idle slots as in the row-per-warp layout), which is what this instruction-issue
+// bound kernel needs (ncu: profiles/r1b_*).
+template <class Tr>
+__device__ __forceinline__ void nn_axis_gaps(int c, float vsize, float q, float (&gap)[3])
+{
+    // squared distance from q to the slab of cell c-1, c, c+1 along one axis (conservative)
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {
+        float lo, hi;
+        Tr::cell_span(c + k - 1, lo, hi);
+        const float eps = (fabsf((float)(c + k - 1)) + 2.0f) * vsize * 1e-6f;
+        const float d   = fmaxf(0.f, fmaxf(lo * vsize - eps - q, q - (hi * vsize + eps)));
+        gap[k]          = d * d * 0.9999f;
+    }
+}
+
+template <class Tr>
+__global__ void __launch_bounds__(256)
+    k_nn_single_pruned(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride,
+                       PoseD pose, int use_pose, float inv, float vsize, QueryOut out)
+{
+    constexpr int CAP = Tr::CAP;
+    for (u32 q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x)
+    {
+        const size_t qi = (size_t)q * stride;
+        float3       p  = make_float3(qx[qi], qy[qi], qz[qi]);
+        if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
+        int        cx, cy, cz;
+        const bool ok = Tr::to_index(p.x, inv, cx) & Tr::to_index(p.y, inv, cy) & Tr::to_index(p.z, inv, cz);
+        float      bd = __int_as_float(0x7f800000);
+        u32        br = 0xFFFFFFFFu, bv = 0;
+        if (ok)
+        {
+            float gx[3], gy[3], gz[3];
+            nn_axis_gaps<Tr>(cx, vsize, p.x, gx);
+            nn_axis_gaps<Tr>(cy, vsize, p.y, gy);
+            nn_axis_gaps<Tr>(cz, vsize, p.z, gz);
+            // visiting order: own voxel (13) first, then the reference's scan order
+#pragma unroll 1
+            for (int it = 0; it < 27; it++)
+            {
+                const int b = it == 0 ? 13 : (it <= 13 ? it - 1 : it);
+                const int ix = b / 9, iy = (b / 3) % 3, iz = b % 3;
+                const float lb = (ix == 0 ? gx[0] : ix == 1 ? gx[1] : gx[2]) + (iy == 0 ? gy[0] : iy == 1 ? gy[1] : gy[2]) +
+                                 (iz == 0 ? gz[0] : iz == 1 ? gz[1] : gz[2]);
+                if (lb > bd) continue;
+                const int x = cx + ix - 1, y = cy + iy - 1, z = cz + iz - 1;
+                if (!index_in_range(x, y, z)) continue;
+                u32 vid, cnt;
+                if (!probe_ro(m.table, m.mask, pack_key(x, y, z), vid, cnt)) continue;
+                const float4* row = m.pts + (size_t)vid * CAP;
+#pragma unroll 4
+                for (u32 s = 0; s < cnt; s++)
+                {
+                    const float4 t    = __ldg(row + s);
+                    const float  d    = sqr_dist(t.x, t.y, t.z, p.x, p.y, p.z);
+                    const u32    rank = (u32)b * 32u + s;
+                    if (d < bd || (d == bd && rank < br)) bd = d, br = rank, bv = vid;
+                }
+            }
+        }
+        const bool found = br != 0xFFFFFFFFu;
+        float4     t     = make_float4(0.f, 0.f, 0.f, 0.f);
+        u64        id    = 0;
+        if (found)
+        {
+            const int b = (int)(br >> 5), slot = (int)(br & 31);
+            t  = __ldg(m.pts + (size_t)bv * CAP + slot);
+            id = plain_id<Tr::SLOT_BITS>(cx + b / 9 - 1, cy + (b / 3) % 3 - 1, cz + b % 3 - 1, slot);
+        }
+        out.found[q]           = found ? 1 : 0;
+        out.xyz[3 * (size_t)q] = t.x, out.xyz[3 * (size_t)q + 1] = t.y, out.xyz[3 * (size_t)q + 2] = t.z;
+        out.d2[q] = found ? bd : 0.f;
+        out.id[q] = id;
     }
 }
 }  // namespace mmg
