@@ -208,6 +208,30 @@ __device__ __forceinline__ void nn_axis_gaps(int c, float vsize, float q, float 
     }
 }
 
+// visits one stencil cell b (0..26) for this thread's query; merges into (bd, br, bv)
+template <class Tr>
+__device__ __forceinline__ void nn_visit_cell(const VoxelMapDev& m, int b, int cx, int cy, int cz, const float3& p, float& bd, u32& br, u32& bv)
+{
+    constexpr int CAP = Tr::CAP;
+    const int     x = cx + b / 9 - 1, y = cy + (b / 3) % 3 - 1, z = cz + b % 3 - 1;
+    if (!index_in_range(x, y, z)) return;
+    u32 vid, cnt;
+    if (!probe_ro(m.table, m.mask, pack_key(x, y, z), vid, cnt)) return;
+    const float4* row = m.pts + (size_t)vid * CAP;
+    // inside a cell the slots come in ascending order, so a strict '<' keeps the first minimum
+    float cd = __int_as_float(0x7f800000);
+    u32   cs = 0;
+#pragma unroll 4
+    for (u32 s = 0; s < cnt; s++)
+    {
+        const float4 t = __ldg(row + s);
+        const float  d = sqr_dist(t.x, t.y, t.z, p.x, p.y, p.z);
+        if (d < cd) cd = d, cs = s;
+    }
+    const u32 rank = (u32)b * 32u + cs;
+    if (cnt && (cd < bd || (cd == bd && rank < br))) bd = cd, br = rank, bv = vid;
+}
+
 template <class Tr>
 __global__ void __launch_bounds__(256)
     k_nn_single_pruned(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride,
@@ -229,28 +253,22 @@ __global__ void __launch_bounds__(256)
             nn_axis_gaps<Tr>(cx, vsize, p.x, gx);
             nn_axis_gaps<Tr>(cy, vsize, p.y, gy);
             nn_axis_gaps<Tr>(cz, vsize, p.z, gz);
-            // visiting order: own voxel (13) first, then the reference's scan order
-#pragma unroll 1
-            for (int it = 0; it < 27; it++)
+            // the query's own voxel first: it nearly always holds the answer and sets the bound
+            nn_visit_cell<Tr>(m, 13, cx, cy, cz, p, bd, br, bv);
+            // this thread's own work list: the neighbours whose box can still matter
+            u32 todo = 0;
+#pragma unroll
+            for (int b = 0; b < 27; b++)
+                if (b != 13 && !(gx[b / 9] + gy[(b / 3) % 3] + gz[b % 3] > bd)) todo |= 1u << b;
+            while (todo)
             {
-                const int b = it == 0 ? 13 : (it <= 13 ? it - 1 : it);
-                const int ix = b / 9, iy = (b / 3) % 3, iz = b % 3;
+                const int b = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const int   ix = b / 9, iy = (b / 3) % 3, iz = b % 3;
                 const float lb = (ix == 0 ? gx[0] : ix == 1 ? gx[1] : gx[2]) + (iy == 0 ? gy[0] : iy == 1 ? gy[1] : gy[2]) +
                                  (iz == 0 ? gz[0] : iz == 1 ? gz[1] : gz[2]);
-                if (lb > bd) continue;
-                const int x = cx + ix - 1, y = cy + iy - 1, z = cz + iz - 1;
-                if (!index_in_range(x, y, z)) continue;
-                u32 vid, cnt;
-                if (!probe_ro(m.table, m.mask, pack_key(x, y, z), vid, cnt)) continue;
-                const float4* row = m.pts + (size_t)vid * CAP;
-#pragma unroll 4
-                for (u32 s = 0; s < cnt; s++)
-                {
-                    const float4 t    = __ldg(row + s);
-                    const float  d    = sqr_dist(t.x, t.y, t.z, p.x, p.y, p.z);
-                    const u32    rank = (u32)b * 32u + s;
-                    if (d < bd || (d == bd && rank < br)) bd = d, br = rank, bv = vid;
-                }
+                if (lb > bd) continue;  // the bound has tightened since the list was made
+                nn_visit_cell<Tr>(m, b, cx, cy, cz, p, bd, br, bv);
             }
         }
         const bool found = br != 0xFFFFFFFFu;
