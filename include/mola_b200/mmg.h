@@ -21,7 +21,7 @@
  *   mmg_nn_radius_batch/_fetch    nn_radius_search        src/HashedVoxelPointCloud.cpp:773-870
  *                                 (SparseVoxel :721-798, SparseTrees :645-713)
  *   mmg_likelihood                internal_computeObservationLikelihoodPointCloud3D  :509-546
- *   mmg_bbox                      boundingBox()           :872-902
+ *   mmg_bbox / mmg_invalidate_bbox  boundingBox() :872-902, cached_.reset() :176
  *   mmg_num_voxels / mmg_export   voxels()/visitAllVoxels/visitAllPoints  :904-919, serializeTo :114-134
  *   mmg_voxel_stats               (extension) per-voxel mean + covariance
  *   mmg_comm_* / mmg_bcast        new: replicate a built map over NCCL (no reference equivalent)
@@ -141,6 +141,8 @@ int mmg_likelihood(const mmg_map* m, const float* xs, const float* ys, const flo
 /* Cached bounding box semantics of the reference (min xyz, max xyz). */
 int mmg_bbox(mmg_map* m, float out_min_max[6]);
 int mmg_is_empty(const mmg_map* m, int* out_empty);
+/* Forgets the cached bounding box (serializeFrom ends with cached_.reset(), HashedVoxelPointCloud.cpp:176). */
+int mmg_invalidate_bbox(mmg_map* m);
 
 /* Export: V voxels, each with its index (cx,cy,cz), its point count and its
  * points in slot order (row stride = mmg_row_capacity(), unused slots zero).

@@ -81,9 +81,40 @@ def build_reference(force=False, verbose=False):
     return out if os.path.exists(out) else None
 
 
+def build_host(force=False, verbose=False, namespace="mola"):
+    """The C++ drop-in classes (mola_b200/host) against the stand-in MRPT headers of shim/mrpt:
+    mola_b200/_lib/libmola_b200_host.so. In a MOLA workspace the same sources build against MRPT."""
+    os.makedirs(LIBDIR, exist_ok=True)
+    out = os.path.join(LIBDIR, "libmola_b200_host.so" if namespace == "mola" else f"libmola_b200_host_{namespace}.so")
+    hdir = os.path.join(ROOT, "mola_b200", "host")
+    srcs = [os.path.join(hdir, "GpuMetricMaps.cpp"), os.path.join(hdir, "register.cpp")]
+    deps = srcs + [os.path.join(hdir, "GpuMetricMaps.h")] + glob.glob(os.path.join(ROOT, "shim", "mrpt", "**", "*.h"), recursive=True)
+    maps = build_maps(force, verbose)
+    if force or _newer(out, deps + [maps]):
+        _run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DMOLA_B200_MRPT_SHIM", f"-DMOLA_B200_NAMESPACE={namespace}",
+              "-I" + os.path.join(ROOT, "shim"), "-I" + os.path.join(ROOT, "include"), "-o", out] + srcs +
+             ["-L" + LIBDIR, "-lmola_b200_maps", "-Wl,-rpath,$ORIGIN"], verbose)
+    return out
+
+
+def build_host_test(force=False, verbose=False):
+    """tests/cpp/test_host_classes.cpp -> tests/cpp/_build/test_host_classes (links the host classes and the C ABI)."""
+    host = build_host(force, verbose, namespace="mola_gpu")
+    tdir = os.path.join(ROOT, "tests", "cpp")
+    os.makedirs(os.path.join(tdir, "_build"), exist_ok=True)
+    out = os.path.join(tdir, "_build", "test_host_classes")
+    src = os.path.join(tdir, "test_host_classes.cpp")
+    if force or _newer(out, [src, host, os.path.join(ROOT, "oracle", "mmo.h")]):
+        _run(["g++", "-O1", "-std=c++17", "-DMOLA_B200_MRPT_SHIM", "-DMOLA_B200_NAMESPACE=mola_gpu", "-I" + os.path.join(ROOT, "shim"),
+              "-I" + os.path.join(ROOT, "include"), "-o", out, src, "-L" + LIBDIR, "-lmola_b200_host_mola_gpu", "-lmola_b200_maps", "-ldl",
+              "-Wl,-rpath," + LIBDIR], verbose)
+    return out
+
+
 def build_all(force=False, verbose=False):
     return {"maps": build_maps(force, verbose), "synth": build_synth(force, verbose),
-            "oracle": build_oracle(force, verbose), "reference": build_reference(force, verbose)}
+            "oracle": build_oracle(force, verbose), "reference": build_reference(force, verbose),
+            "host": build_host(force, verbose), "host_test": build_host_test(force, verbose)}
 
 
 if __name__ == "__main__":

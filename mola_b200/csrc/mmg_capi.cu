@@ -682,6 +682,14 @@ int mmg_bbox(mmg_map* m, float out[6])
     return MMG_OK;
 }
 
+int mmg_invalidate_bbox(mmg_map* m)
+{
+    MMG_CHECK_MAP(m);
+    u32 b[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
+    MMG_CUDA(cudaMemcpy(m->dev.ctr->bbox, b, sizeof(b), cudaMemcpyHostToDevice));
+    return MMG_OK;
+}
+
 int mmg_num_voxels(const mmg_map* m, uint64_t* out_v)
 {
     if (!m || !out_v) return MMG_ERR_INVALID_ARG;
