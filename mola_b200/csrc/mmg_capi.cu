@@ -60,6 +60,20 @@ void* mmg_map::scratch_get(int slot, size_t bytes)
     return s.first;
 }
 
+int mmg_map::ensure_pipeline()
+{
+    if (s_in) return MMG_OK;
+    MMG_CUDA(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
+    MMG_CUDA(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+    MMG_CUDA(cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming));
+    for (int i = 0; i < 8; i++)
+    {
+        MMG_CUDA(cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming));
+        MMG_CUDA(cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming));
+    }
+    return MMG_OK;
+}
+
 static int init_counters(mmg_map* m, bool keep_bbox)
 {
     Counters c;
@@ -265,24 +279,9 @@ struct OutBufs
 };
 
 template <class Tr>
-static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, size_t stride, const double* pose12,
-                           uint8_t* ofound, float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st)
+static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy, const float* dz, size_t nq, size_t stride, const PoseD& T, int use_pose,
+                             const QueryOut& o, cudaStream_t st)
 {
-    mmg_map* m = const_cast<mmg_map*>(cm);
-    if (n == 0) return MMG_OK;
-    const size_t nq = (n + stride - 1) / stride;
-    const float *dx, *dy, *dz;
-    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
-    if (rc) return rc;
-    QueryOut o{ofound, oxyz, od2, (u64*)oid};
-    char*    ob = nullptr;
-    if (mem == MMG_MEM_HOST)
-    {
-        ob = (char*)m->scratch_get(S_OUT, nq * 32);
-        if (!ob) return MMG_ERR_OUT_OF_MEM;
-        o.id = (u64*)ob, o.xyz = (float*)(ob + nq * 8), o.d2 = (float*)(ob + nq * 20), o.found = (uint8_t*)(ob + nq * 24);
-    }
-    const PoseD    T  = make_pose(pose12);
     // A/B switch for the profiles: MMG_NN_KERNEL = pruned (default) | grouped | simple
     static const int variant = [] {
         const char* e = getenv("MMG_NN_KERNEL");
@@ -291,27 +290,77 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
     if (variant == 2)
     {
         const unsigned nb = persistent_blocks(m, nq, 8, 8);
-        MMG_LAUNCH((k_nn_single<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, o);
+        MMG_LAUNCH((k_nn_single<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, o);
     }
     else if (variant == 1)
     {
         const unsigned nb = persistent_blocks(m, (nq + 31) / 32, 8, 8);
-        MMG_LAUNCH((k_nn_single_grouped<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, m->prm.voxel_size, o);
+        MMG_LAUNCH((k_nn_single_grouped<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o);
     }
     else
     {
         const unsigned nb = (unsigned)std::min<size_t>((nq + 255) / 256, (size_t)m->num_sms * 64);
-        MMG_LAUNCH((k_nn_single_pruned<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, m->inv, m->prm.voxel_size, o);
+        MMG_LAUNCH((k_nn_single_pruned<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o);
+    }
+}
+
+template <class Tr>
+static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, size_t stride, const double* pose12,
+                           uint8_t* ofound, float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st)
+{
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (n == 0) return MMG_OK;
+    const size_t nq = (n + stride - 1) / stride;
+    const PoseD  T  = make_pose(pose12);
+    if (mem == MMG_MEM_DEVICE)
+    {
+        launch_nn_single<Tr>(m, xs, ys, zs, nq, stride, T, pose12 ? 1 : 0, QueryOut{ofound, oxyz, od2, (u64*)oid}, st);
+        MMG_CUDA(cudaGetLastError());
+        return MMG_OK;
+    }
+    // Host buffers: the batch is cut into up to 8 chunks and the three stages run on three streams,
+    // so the H2D copy of chunk c+1, the kernel of chunk c and the D2H copy of chunk c-1 overlap
+    // (PCIe is full duplex; the kernel is far shorter than either copy).
+    if (stride != 1)
+    {
+        set_error("strided queries take device buffers");
+        return MMG_ERR_INVALID_ARG;
+    }
+    int rc = m->ensure_pipeline();
+    if (rc) return rc;
+    float* b  = (float*)m->scratch_get(S_IN, 3 * n * sizeof(float));
+    char*  ob = (char*)m->scratch_get(S_OUT, nq * 32);
+    if (!b || !ob) return MMG_ERR_OUT_OF_MEM;
+    u64*     did  = (u64*)ob;
+    float*   dxyz = (float*)(ob + nq * 8);
+    float*   dd2  = (float*)(ob + nq * 20);
+    uint8_t* dfn  = (uint8_t*)(ob + nq * 24);
+    size_t   ch   = std::max<size_t>(65536, (nq + 3) / 4);
+    ch            = (ch + 255) / 256 * 256;
+    if ((nq + ch - 1) / ch > 8) ch = ((nq + 7) / 8 + 255) / 256 * 256;
+    MMG_CUDA(cudaEventRecord(m->ev_start, st));
+    MMG_CUDA(cudaStreamWaitEvent(m->s_in, m->ev_start, 0));
+    MMG_CUDA(cudaStreamWaitEvent(m->s_out, m->ev_start, 0));
+    int c = 0;
+    for (size_t a = 0; a < nq; a += ch, c++)
+    {
+        const size_t k = std::min(ch, nq - a);
+        MMG_CUDA(cudaMemcpyAsync(b + a, xs + a, k * sizeof(float), cudaMemcpyHostToDevice, m->s_in));
+        MMG_CUDA(cudaMemcpyAsync(b + n + a, ys + a, k * sizeof(float), cudaMemcpyHostToDevice, m->s_in));
+        MMG_CUDA(cudaMemcpyAsync(b + 2 * n + a, zs + a, k * sizeof(float), cudaMemcpyHostToDevice, m->s_in));
+        MMG_CUDA(cudaEventRecord(m->ev_in[c], m->s_in));
+        MMG_CUDA(cudaStreamWaitEvent(st, m->ev_in[c], 0));
+        launch_nn_single<Tr>(m, b + a, b + n + a, b + 2 * n + a, k, 1, T, pose12 ? 1 : 0, QueryOut{dfn + a, dxyz + 3 * a, dd2 + a, did + a}, st);
+        MMG_CUDA(cudaEventRecord(m->ev_k[c], st));
+        MMG_CUDA(cudaStreamWaitEvent(m->s_out, m->ev_k[c], 0));
+        MMG_CUDA(cudaMemcpyAsync(oxyz + 3 * a, dxyz + 3 * a, k * 12, cudaMemcpyDeviceToHost, m->s_out));
+        MMG_CUDA(cudaMemcpyAsync(oid + a, did + a, k * 8, cudaMemcpyDeviceToHost, m->s_out));
+        MMG_CUDA(cudaMemcpyAsync(od2 + a, dd2 + a, k * 4, cudaMemcpyDeviceToHost, m->s_out));
+        MMG_CUDA(cudaMemcpyAsync(ofound + a, dfn + a, k, cudaMemcpyDeviceToHost, m->s_out));
     }
     MMG_CUDA(cudaGetLastError());
-    if (mem == MMG_MEM_HOST)
-    {
-        MMG_CUDA(cudaMemcpyAsync(oid, o.id, nq * 8, cudaMemcpyDeviceToHost, st));
-        MMG_CUDA(cudaMemcpyAsync(oxyz, o.xyz, nq * 12, cudaMemcpyDeviceToHost, st));
-        MMG_CUDA(cudaMemcpyAsync(od2, o.d2, nq * 4, cudaMemcpyDeviceToHost, st));
-        MMG_CUDA(cudaMemcpyAsync(ofound, o.found, nq, cudaMemcpyDeviceToHost, st));
-        MMG_CUDA(cudaStreamSynchronize(st));
-    }
+    MMG_CUDA(cudaStreamSynchronize(m->s_out));
+    MMG_CUDA(cudaStreamSynchronize(st));
     return MMG_OK;
 }
 
@@ -462,6 +511,11 @@ int mmg_destroy(mmg_map* m)
     cudaFree(m->dev.table), cudaFree(m->dev.pts), cudaFree(m->dev.cnt), cudaFree(m->dev.vkey), cudaFree(m->dev.mean), cudaFree(m->dev.free_list),
         cudaFree(m->dev.ctr);
     if (m->h_ctr) cudaFreeHost(m->h_ctr);
+    if (m->s_in)
+    {
+        cudaStreamDestroy(m->s_in), cudaStreamDestroy(m->s_out), cudaEventDestroy(m->ev_start);
+        for (int i = 0; i < 8; i++) cudaEventDestroy(m->ev_in[i]), cudaEventDestroy(m->ev_k[i]);
+    }
     for (auto& s : m->scratch)
         if (s.first) cudaFree(s.first);
     delete m;

@@ -64,6 +64,10 @@ struct mmg_map
     float *   rad_xyz = nullptr, *rad_d2 = nullptr;
     // SparseTrees
     mmg::TreesState* trees = nullptr;
+    // host-buffer pipeline (H2D | kernel | D2H overlapped in chunks), created on first use
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t  ev_start = nullptr, ev_in[8] = {}, ev_k[8] = {};
+    int          ensure_pipeline();
     // grow-only device scratch
     std::vector<std::pair<void*, size_t>> scratch;
     void*                                 scratch_get(int slot, size_t bytes);
