@@ -167,6 +167,43 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def bench_batch_insert(args, dev, local_rank, stream):
+    """Insert throughput on a batch large enough to be bandwidth- rather than launch-bound: BASELINE config 5's shape,
+    `--insert-scans` OS1-128 scans (262,144 points each, 2 m apart) inserted by ONE mmg_insert_scans call into an empty
+    HashedVoxelPointCloud, inputs resident in HBM, CUDA-event time. Algorithmic bytes/point = 36 + 12*a."""
+    import torch
+    from mola_b200 import HashedVoxelPointCloud, synth
+    ns = args.insert_scans
+    if ns <= 0:
+        return None
+    scans = [synth.lidar_scan("os1_128", s=2.0 * k, seed=5, scan_id=k) for k in range(ns)]
+    off = np.concatenate([[0], np.cumsum([s[0].size for s in scans])]).astype(np.uint64)
+    poses = np.stack([s[3] for s in scans])
+    d = [torch.from_numpy(np.concatenate([s[a] for s in scans])).to(dev) for a in range(3)]
+    best, stored = None, 0
+    for rep in range(3):
+        m = HashedVoxelPointCloud(VOXEL, device=local_rank)
+        if rep == 0:
+            m.insertPointClouds(d[0][:1000], d[1][:1000], d[2][:1000], np.array([0, 1000], np.uint64), poses[:1])  # allocations
+            m.clear()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        m.insertPointClouds(d[0], d[1], d[2], off, poses)
+        e1.record(stream)
+        e1.synchronize()
+        ms = e0.elapsed_time(e1)
+        best = ms if best is None else min(best, ms)
+        stored = m.numPoints()
+        del m
+    n = int(off[-1])
+    a = stored / n
+    bpp = 36.0 + 12.0 * a
+    return {"mpts_s": n / (best * 1e-3) / 1e6, "points_in": n, "scans": ns, "stored_points": int(stored), "accepted_frac": a,
+            "ms": best, "algorithmic_bytes_per_point": bpp, "achieved_gbs": bpp * n / (best * 1e-3) / 1e9,
+            "note": "one mmg_insert_scans call (k_insert_rank + k_insert_commit per <=1M-point chunk), empty map, best of 3"}
+
+
 def run_gpu(args, rank, world, local_rank):
     import ctypes as C
     import torch
@@ -182,6 +219,9 @@ def run_gpu(args, rank, world, local_rank):
     stream = torch.cuda.current_stream(dev)
     sp = C.c_void_p(stream.cuda_stream)
 
+    if args.only == "insert_batched":  # profiling aid: just the batched-insert leg
+        print(json.dumps({"insert_batched": bench_batch_insert(args, dev, local_rank, stream)}), flush=True)
+        return
     # ---- map build (rank 0), CPU twin for the cpu_baseline leg (rank 0, N == 1) ----------------
     want_cpu = (rank == 0 and world == 1 and not args.no_cpu)
     om = None
@@ -217,6 +257,7 @@ def run_gpu(args, rank, world, local_rank):
     else:
         bcast_s = 0.0
     stats = gmap.tableStats()
+    batch_insert = bench_batch_insert(args, dev, local_rank, stream) if rank == 0 else None
 
     # ---- queries ---------------------------------------------------------------------------
     q = query_batch(nscans, rank)
@@ -302,6 +343,8 @@ def run_gpu(args, rank, world, local_rank):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     bytes_per_q = 361.0 + 12.0 * pbar.value
+    if batch_insert:
+        batch_insert["frac_of_hbm_peak"] = batch_insert["achieved_gbs"] / peak
     achieved = bytes_per_q * n / (dev_ms / args.steps * 1e-3) / 1e9
     traffic = None
     try:
@@ -318,11 +361,12 @@ def run_gpu(args, rank, world, local_rank):
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": 12 * n, "d2h_bytes_per_step": 25 * n},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "kernel": "k_nn_single<HashedTraits>", "algorithmic_bytes_per_query": bytes_per_q, "mean_stencil_points": pbar.value,
+                         "kernel": "k_nn_single_pruned<HashedTraits>", "algorithmic_bytes_per_query": bytes_per_q, "mean_stencil_points": pbar.value,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650"},
             "clocks": clocks, "found_frac": found_frac, "wall_ms_per_step_incl_flush": 1e3 * wall_s / args.steps,
             "insert": {"mpts_s": n_in / (ins_ms[0] * 1e-3) / 1e6 if ins_ms[0] else None, "points_in": n_in, "scans": nscans,
                        "note": "per-scan batches of 120k points, device-resident inputs, CUDA-event time"},
+            "insert_batched": batch_insert,
             "table": {k: stats[k] for k in ("capacity", "load_factor", "mean_probe", "max_probe")},
             "bcast_s": bcast_s, "setup_s": time.perf_counter() - t_setup}
     if om is not None:
@@ -345,7 +389,9 @@ def main():
     ap.add_argument("--map-points", type=int, default=MAP_POINTS)
     ap.add_argument("--cpu-sample", type=int, default=200_000)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--insert-scans", type=int, default=64, help="OS1-128 scans in the batched-insert measurement (0 = skip)")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--only", default="", choices=["", "insert_batched"], help="profiling aid: run one leg only")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":

@@ -113,6 +113,15 @@ int mmg_get_params(const mmg_map* m, mmg_params* p);
 int mmg_insert_batch(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n,
                      const double* pose12, int has_robot_pose, int mem, void* stream);
 
+/* Several scans in one call: scan s = points [scan_offsets[s], scan_offsets[s+1]) with pose
+ * poses12 + 12*s (scan_offsets and poses12 are HOST arrays; the points follow `mem`).
+ * Identical to calling mmg_insert_batch once per scan in order (the reference's
+ * insertObservation loop, src/HashedVoxelPointCloud.cpp:289-331); when no eviction or
+ * min-distance test is configured the scans are ranked in one fused pass on the device. */
+int mmg_insert_scans(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n_scans,
+                     const uint64_t* scan_offsets /*n_scans+1*/, const double* poses12 /*n_scans*12*/,
+                     int has_robot_pose, int mem, void* stream);
+
 /* out_found[n] (0/1), out_xyz[n*3], out_d2[n], out_id[n]. Entries of not-found
  * queries are zero. */
 int mmg_nn_single_batch(const mmg_map* m, const float* xs, const float* ys, const float* zs,

@@ -5,6 +5,7 @@
 #include "../../include/mola_b200/mmg.h"
 #include "mmg_host.h"
 #include "mmg_query.cuh"
+#include "mmg_insert.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -192,27 +193,73 @@ unsigned mmg::persistent_blocks(const mmg_map* m, size_t work_warps, int warps_p
 }
 
 // ------------------------------------------------------------------ insert
+static int evict_far(mmg_map* m, const double* pose12, cudaStream_t st)
+{   // far-voxel eviction, HashedVoxelPointCloud.cpp:305-326 (Hashed only)
+    const mmg_params& P            = m->prm;
+    const int         dist_in_grid = (int)std::ceil(P.remove_voxels_farther_than * (double)m->inv);
+    const float       t[3]         = {(float)pose12[9], (float)pose12[10], (float)pose12[11]};
+    const int         ox = (int)(t[0] * m->inv), oy = (int)(t[1] * m->inv), oz = (int)(t[2] * m->inv);
+    MMG_LAUNCH(k_evict, (m->h_nvox_hi + 255) / 256, 256, 0, st, m->dev, m->h_nvox_hi, ox, oy, oz, dist_in_grid);
+    Counters c;
+    int      rc = read_counters(m, &c, st);
+    if (rc) return rc;
+    if (c.free_n != m->h_free_n)
+    {  // something was evicted: rebuild the (tombstone-free) table from the live rows
+        m->h_free_n = c.free_n;
+        MMG_CUDA(cudaMemsetAsync(m->dev.table, 0xFF, m->cap * sizeof(Entry), st));
+        MMG_LAUNCH(k_rebuild_table, (m->h_nvox_hi + 255) / 256, 256, 0, st, m->dev, m->h_nvox_hi);
+    }
+    return MMG_OK;
+}
+
+// Cap-only decimation (min_distance_between_points == 0): the sort-free path of mmg_insert.cuh.
+// The batch is cut into chunks so that the worst case "every point opens a new voxel" bounds the
+// table and row growth per chunk; one 64-byte counter read-back per chunk is the only sync.
+template <class Tr>
+static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const float* dz, size_t n, const ScanSet& S0, cudaStream_t st, u32* oob_out)
+{
+    const mmg_params& P        = m->prm;
+    const u32         hard     = (u32)Tr::CAP;
+    const bool        uncapped = (P.max_points_per_voxel == 0 || P.max_points_per_voxel > hard);
+    const u32         eff      = uncapped ? hard : P.max_points_per_voxel;
+    MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->oob, 0, sizeof(u32), st));
+    Counters c;
+    memset(&c, 0, sizeof(c));
+    for (size_t a = 0; a < n;)
+    {
+        const u64    live = m->h_nvox_hi - m->h_free_n;
+        const size_t k    = std::min<size_t>(n - a, std::max<u64>(1u << 20, 4 * live));
+        int          rc;
+        if ((rc = ensure_table(m, live + k, st))) return rc;
+        if ((rc = ensure_rows(m, (u64)m->h_nvox_hi + k, st))) return rc;
+        u32* touched = (u32*)m->scratch_get(S_SEG, k * sizeof(u32));
+        if (!touched) return MMG_ERR_OUT_OF_MEM;
+        MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->nseg, 0, sizeof(u32), st));
+        ScanSet S = S0;
+        MMG_LAUNCH((k_insert_rank<Tr>), (unsigned)((k + 255) / 256), 256, 0, st, dx + a, dy + a, dz + a, (u32)k, (u32)a, S, m->inv, m->dev, eff, touched,
+                   uncapped ? 1 : 0);
+        const unsigned fb = persistent_blocks(m, k, 8, 8);
+        MMG_LAUNCH((k_insert_commit<Tr>), fb, 256, 0, st, m->dev, touched, dx + a, dy + a, dz + a, (u32)a, S, m->inv, uncapped ? 0 : 1,
+                   m->kind == MMG_SPARSE_VOXEL ? 1 : 0);
+        MMG_CUDA(cudaGetLastError());
+        if ((rc = read_counters(m, &c, st))) return rc;
+        m->h_nvox_hi = c.nvox_hi;
+        m->h_free_n  = c.free_n;
+        a += k;
+    }
+    *oob_out = c.oob;
+    return MMG_OK;
+}
+
 template <class Tr>
 static int insert_voxel(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, int has_robot_pose, int mem,
                         cudaStream_t st)
 {
     const mmg_params& P = m->prm;
-    // far-voxel eviction, HashedVoxelPointCloud.cpp:305-326 (Hashed only)
     if (m->kind == MMG_HASHED_VOXEL && has_robot_pose && pose12 && P.remove_voxels_farther_than > 0 && m->h_nvox_hi > 0)
     {
-        const int   dist_in_grid = (int)std::ceil(P.remove_voxels_farther_than * (double)m->inv);
-        const float t[3]         = {(float)pose12[9], (float)pose12[10], (float)pose12[11]};
-        const int   ox = (int)(t[0] * m->inv), oy = (int)(t[1] * m->inv), oz = (int)(t[2] * m->inv);
-        MMG_LAUNCH(k_evict, (m->h_nvox_hi + 255) / 256, 256, 0, st, m->dev, m->h_nvox_hi, ox, oy, oz, dist_in_grid);
-        Counters c;
-        int      rc = read_counters(m, &c, st);
+        int rc = evict_far(m, pose12, st);
         if (rc) return rc;
-        if (c.free_n != m->h_free_n)
-        {  // something was evicted: rebuild the (tombstone-free) table from the live rows
-            m->h_free_n = c.free_n;
-            MMG_CUDA(cudaMemsetAsync(m->dev.table, 0xFF, m->cap * sizeof(Entry), st));
-            MMG_LAUNCH(k_rebuild_table, (m->h_nvox_hi + 255) / 256, 256, 0, st, m->dev, m->h_nvox_hi);
-        }
     }
     if (n == 0) return MMG_OK;
     if (n >= (1ull << 31))
@@ -223,6 +270,23 @@ static int insert_voxel(mmg_map* m, const float* xs, const float* ys, const floa
     const float *dx, *dy, *dz;
     int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
     if (rc) return rc;
+    const bool  min_dist  = (m->kind == MMG_HASHED_VOXEL) && P.min_distance_between_points > 0.f;
+    const float thr       = min_dist ? P.min_distance_between_points * P.min_distance_between_points : 0.f;
+    const bool  use_thr   = min_dist && thr > 0.f;
+    static const bool force_sorted = getenv("MMG_INSERT_SORTED") != nullptr;  // A/B switch for the profiles
+    if (!use_thr && !force_sorted)
+    {
+        ScanSet S{nullptr, nullptr, 1, make_pose(pose12)};
+        u32     oob = 0;
+        if ((rc = insert_ranked<Tr>(m, dx, dy, dz, n, S, st, &oob))) return rc;
+        m->points_dirty = true;
+        if (oob)
+        {
+            set_error("%u of %zu points have a voxel index outside +-2^20 and were skipped", oob, n);
+            return MMG_ERR_OUT_OF_RANGE;
+        }
+        return MMG_OK;
+    }
     const u64 live = m->h_nvox_hi - m->h_free_n;
     if ((rc = ensure_table(m, live + n, st))) return rc;
 
@@ -235,9 +299,6 @@ static int insert_voxel(mmg_map* m, const float* xs, const float* ys, const floa
     SortScratch ss{sbuf, sbuf + n, sbuf + 2 * n, sbuf + 3 * n, sbuf + 3 * n + (size_t)RS_RADIX * nb};
 
     const u32   hard      = (u32)Tr::CAP;
-    const bool  min_dist  = (m->kind == MMG_HASHED_VOXEL) && P.min_distance_between_points > 0.f;
-    const float thr       = min_dist ? P.min_distance_between_points * P.min_distance_between_points : 0.f;
-    const bool  use_thr   = min_dist && thr > 0.f;
     const bool  uncapped  = (P.max_points_per_voxel == 0 || P.max_points_per_voxel > hard);
     const int   bbox_all  = (!use_thr && uncapped) ? 1 : 0;
     const int   bbox_acc  = (!use_thr && !uncapped) ? 1 : 0;
@@ -570,6 +631,64 @@ int mmg_insert_batch(mmg_map* m, const float* xs, const float* ys, const float* 
         case MMG_SPARSE_VOXEL: return insert_voxel<SparseVoxelTraits>(m, xs, ys, zs, n, pose12, has_robot_pose, mem, st);
         default: return trees_insert(m, xs, ys, zs, n, pose12, has_robot_pose, mem, st);
     }
+}
+
+int mmg_insert_scans(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n_scans, const uint64_t* scan_offsets,
+                     const double* poses12, int has_robot_pose, int mem, void* stream)
+{
+    MMG_CHECK_MAP(m);
+    if (n_scans == 0) return MMG_OK;
+    if (!scan_offsets || !poses12) return MMG_ERR_INVALID_ARG;
+    const size_t n = scan_offsets[n_scans] - scan_offsets[0];
+    if (n && (!xs || !ys || !zs)) return MMG_ERR_INVALID_ARG;
+    for (size_t s = 0; s < n_scans; s++)
+        if (scan_offsets[s + 1] < scan_offsets[s])
+        {
+            set_error("scan_offsets must ascend");
+            return MMG_ERR_INVALID_ARG;
+        }
+    cudaStream_t      st = (cudaStream_t)stream;
+    const mmg_params& P  = m->prm;
+    // One fused pass is only equivalent to scan-by-scan insertion when nothing happens between the scans
+    // (no eviction) and the per-voxel rule is the cap-only one; otherwise insert scan by scan.
+    const bool evicts = has_robot_pose && P.remove_voxels_farther_than > 0 && m->kind != MMG_SPARSE_VOXEL;
+    const bool fused  = m->kind != MMG_SPARSE_TREES && !evicts && !(m->kind == MMG_HASHED_VOXEL && P.min_distance_between_points > 0.f) &&
+                       n < (1ull << 31) && scan_offsets[0] == 0;
+    if (!fused)
+    {
+        int worst = MMG_OK;
+        for (size_t s = 0; s < n_scans; s++)
+        {
+            const size_t a = scan_offsets[s], k = scan_offsets[s + 1] - a;
+            const int    rc = mmg_insert_batch(m, xs + a, ys + a, zs + a, k, poses12 + 12 * s, has_robot_pose, mem, stream);
+            if (rc == MMG_ERR_OUT_OF_RANGE) worst = rc;
+            else if (rc) return rc;
+        }
+        return worst;
+    }
+    if (n == 0) return MMG_OK;
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    char* sb = (char*)m->scratch_get(S_SCANS, n_scans * sizeof(PoseD) + (n_scans + 1) * sizeof(u32));
+    if (!sb) return MMG_ERR_OUT_OF_MEM;
+    std::vector<u32> off(n_scans + 1);
+    for (size_t s = 0; s <= n_scans; s++) off[s] = (u32)scan_offsets[s];
+    MMG_CUDA(cudaMemcpyAsync(sb, poses12, n_scans * sizeof(PoseD), cudaMemcpyHostToDevice, st));
+    MMG_CUDA(cudaMemcpyAsync(sb + n_scans * sizeof(PoseD), off.data(), (n_scans + 1) * sizeof(u32), cudaMemcpyHostToDevice, st));
+    MMG_CUDA(cudaStreamSynchronize(st));  // `off` is pageable and about to go out of scope
+    ScanSet S{(const PoseD*)sb, (const u32*)(sb + n_scans * sizeof(PoseD)), (u32)n_scans, make_pose(nullptr)};
+    u32     oob = 0;
+    if (m->kind == MMG_HASHED_VOXEL) rc = insert_ranked<HashedTraits>(m, dx, dy, dz, n, S, st, &oob);
+    else rc = insert_ranked<SparseVoxelTraits>(m, dx, dy, dz, n, S, st, &oob);
+    if (rc) return rc;
+    m->points_dirty = true;
+    if (oob)
+    {
+        set_error("%u of %zu points have a voxel index outside +-2^20 and were skipped", oob, n);
+        return MMG_ERR_OUT_OF_RANGE;
+    }
+    return MMG_OK;
 }
 
 int mmg_nn_single_batch(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, uint8_t* out_found,

@@ -38,6 +38,7 @@ enum ScratchSlot
     S_HSORT,
     S_QID,
     S_LIK,
+    S_SCANS,
     S_TREES0,
     S_TREES1,
     S_TREES2,

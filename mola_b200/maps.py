@@ -133,6 +133,21 @@ class _Map:
         capi.check(rc, allow=(capi.MMG_ERR_OUT_OF_RANGE,))
         return rc == capi.MMG_ERR_OUT_OF_RANGE
 
+    def insertPointClouds(self, xs, ys, zs, scan_offsets, robotPoses, with_eviction=True):
+        """A sequence of insertObservation calls in one batch: scan s is points
+        [scan_offsets[s], scan_offsets[s+1]) with pose robotPoses[s] (12 doubles each). Same result as
+        calling insertPointCloud once per scan in order; fused into one device pass when the options
+        allow it (mmg_insert_scans)."""
+        self._sync_params()
+        mem, st, keep, px, py, pz, n, _ = self._xyz(xs, ys, zs)
+        off = np.ascontiguousarray(scan_offsets, dtype=np.uint64)
+        poses = np.ascontiguousarray(np.asarray(robotPoses, dtype=np.float64).reshape(-1, 12))
+        assert off.ndim == 1 and off.size == poses.shape[0] + 1 and int(off[-1]) - int(off[0]) <= n
+        rc = self._lib.mmg_insert_scans(self._h, px, py, pz, C.c_size_t(poses.shape[0]), off.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                        poses.ctypes.data_as(C.POINTER(C.c_double)), 1 if with_eviction else 0, mem, st)
+        capi.check(rc, allow=(capi.MMG_ERR_OUT_OF_RANGE,))
+        return rc == capi.MMG_ERR_OUT_OF_RANGE
+
     def internal_insertPointCloud3D(self, pc_in_map, xs, ys, zs):
         """The reference's private helper (:1065-1082): compose + insert, no eviction."""
         self._sync_params()

@@ -203,3 +203,67 @@ def test_edge_cases(built):
     assert g3.insertPointCloud(y, y, y) is True
     o3.insert(y[[0, 3]], y[[0, 3]], y[[0, 3]])
     assert_same_map(g3, o3)
+
+
+def _scan_batch(n_scans, sensor="tiny", step=2.0):
+    scans = [_scan(sensor, s=step * k, scan_id=k) for k in range(n_scans)]
+    xs, ys, zs = (np.concatenate([s[a] for s in scans]) for a in range(3))
+    off = np.concatenate([[0], np.cumsum([s[0].size for s in scans])]).astype(np.uint64)
+    poses = np.stack([s[3] for s in scans])
+    return scans, xs, ys, zs, off, poses
+
+
+@pytest.mark.parametrize("opts", [dict(), dict(max_points_per_voxel=5), dict(max_points_per_voxel=40),
+                                  dict(min_distance_between_points=0.05), dict(remove_voxels_farther_than=15.0)])
+def test_insert_scans_equals_sequential(built, opts):
+    """mmg_insert_scans (one fused device pass when the options allow it, scan by scan otherwise) ==
+    insertObservation once per scan in order (HashedVoxelPointCloud.cpp:289-331)."""
+    g, o = _maps(0.5, **opts)
+    scans, xs, ys, zs, off, poses = _scan_batch(5, "tiny", step=4.0)
+    # a map that already holds something, so n0 > 0 rows are exercised too
+    g.insertPointCloud(*scans[2])
+    o.insert(*scans[2])
+    g.insertPointClouds(xs, ys, zs, off, poses)
+    for s in scans:
+        o.insert(*s)
+    assert_same_map(g, o)
+    gmin, gmax = g.boundingBox()
+    omin, omax = o.bbox()
+    assert np.array_equal(gmin, omin) and np.array_equal(gmax, omax)
+
+
+def test_insert_scans_hdl64_and_device_buffers(built):
+    """Four 120k-pt scans in one call, device-resident inputs, then nn_single parity on the result."""
+    import torch
+    g, o = _maps(0.5)
+    scans, xs, ys, zs, off, poses = _scan_batch(4, "hdl64", step=3.0)
+    d = [torch.from_numpy(a).cuda() for a in (xs, ys, zs)]
+    g.insertPointClouds(d[0], d[1], d[2], off, poses)
+    for s in scans:
+        o.insert(*s)
+    assert_same_map(g, o)
+    # the ranking scratch (float4.w of free slots) must be clean again: a second batch still matches
+    g.insertPointClouds(d[0], d[1], d[2], off, poses)
+    for s in scans:
+        o.insert(*s)
+    assert_same_map(g, o)
+    qx, qy, qz = compose_host(poses[1], scans[1][0] + np.float32(0.07), scans[1][1], scans[1][2])
+    _check_nn_single(g, o, qx[:50000], qy[:50000], qz[:50000])
+
+
+def test_insert_adversarial_order(built):
+    """Ranking stress: many points of few voxels in shuffled order, duplicates, a voxel filled across
+    several batches and partially filled rows."""
+    rng = np.random.default_rng(5)
+    g, o = _maps(1.0)
+    for it in range(4):
+        n = 40000
+        cells = rng.integers(0, 6, size=(n, 3)).astype(np.float32)
+        p = cells + rng.random((n, 3), dtype=np.float32) * np.float32(0.9) + np.float32(0.05)
+        p[::7] = p[3]  # exact duplicates
+        if it == 0:
+            p = p[:50]  # leaves partially filled rows for the next batches
+        x, y, z = (np.ascontiguousarray(p[:, a]) for a in range(3))
+        g.insertPointCloud(x, y, z)
+        o.insert(x, y, z)
+        assert_same_map(g, o)
