@@ -180,12 +180,10 @@ def bench_batch_insert(args, dev, local_rank, stream):
     off = np.concatenate([[0], np.cumsum([s[0].size for s in scans])]).astype(np.uint64)
     poses = np.stack([s[3] for s in scans])
     d = [torch.from_numpy(np.concatenate([s[a] for s in scans])).to(dev) for a in range(3)]
-    best, stored = None, 0
-    for rep in range(3):
-        m = HashedVoxelPointCloud(VOXEL, device=local_rank)
-        if rep == 0:
-            m.insertPointClouds(d[0][:1000], d[1][:1000], d[2][:1000], np.array([0, 1000], np.uint64), poses[:1])  # allocations
-            m.clear()
+    best, cold, stored = None, None, 0
+    m = HashedVoxelPointCloud(VOXEL, device=local_rank)
+    for rep in range(4):  # rep 0 = cold (table / row-store growth inside the timed region), then clear() + re-insert
+        m.clear()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
@@ -193,15 +191,18 @@ def bench_batch_insert(args, dev, local_rank, stream):
         e1.record(stream)
         e1.synchronize()
         ms = e0.elapsed_time(e1)
-        best = ms if best is None else min(best, ms)
+        if rep == 0:
+            cold = ms
+        else:
+            best = ms if best is None else min(best, ms)
         stored = m.numPoints()
-        del m
+    del m
     n = int(off[-1])
     a = stored / n
     bpp = 36.0 + 12.0 * a
     return {"mpts_s": n / (best * 1e-3) / 1e6, "points_in": n, "scans": ns, "stored_points": int(stored), "accepted_frac": a,
-            "ms": best, "algorithmic_bytes_per_point": bpp, "achieved_gbs": bpp * n / (best * 1e-3) / 1e9,
-            "note": "one mmg_insert_scans call (k_insert_rank + k_insert_commit per <=1M-point chunk), empty map, best of 3"}
+            "ms": best, "ms_cold_map": cold, "algorithmic_bytes_per_point": bpp, "achieved_gbs": bpp * n / (best * 1e-3) / 1e9,
+            "note": "one mmg_insert_scans call (k_insert_rank + k_insert_commit per chunk), cleared map with its row store kept (ms_cold_map: first insert into a new map, allocation included), best of 3"}
 
 
 def run_gpu(args, rank, world, local_rank):

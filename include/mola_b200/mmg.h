@@ -107,6 +107,10 @@ int mmg_clone(const mmg_map* m, mmg_map** out);
 int mmg_set_params(mmg_map* m, const mmg_params* p);
 int mmg_get_params(const mmg_map* m, mmg_params* p);
 
+/* Pre-sizes the hash table (load <= 0.5) and the row store for `voxels` voxels, like the
+ * reference's voxels_.reserve() (src/HashedVoxelPointCloud.cpp:1070). Optional: inserts grow both on demand. */
+int mmg_reserve(mmg_map* m, uint64_t voxels);
+
 /* Inserts n points in input order (per-voxel decimation identical to calling the
  * reference's insertPoint once per point). has_robot_pose!=0 enables the
  * far-voxel eviction step with pose12's translation as the sensor position. */

@@ -228,7 +228,11 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
     for (size_t a = 0; a < n;)
     {
         const u64    live = m->h_nvox_hi - m->h_free_n;
-        const size_t k    = std::min<size_t>(n - a, std::max<u64>(1u << 20, 4 * live));
+        // chunk: at least 1M points; up to 4M for big batches (worst case 2 GB of row headroom); more when the map is
+        // already large or was reserved (mmg_reserve) for more
+        const u64    room_rows = m->rowcap > m->h_nvox_hi ? m->rowcap - m->h_nvox_hi : 0;
+        const u64    room_tab  = m->cap / 2 > live ? m->cap / 2 - live : 0;
+        const size_t k = std::min<size_t>(n - a, std::max<u64>({(u64)1 << 20, 4 * live, std::min<u64>((n - a + 3) / 4, (u64)4 << 20), std::min(room_rows, room_tab)}));
         int          rc;
         if ((rc = ensure_table(m, live + k, st))) return rc;
         if ((rc = ensure_rows(m, (u64)m->h_nvox_hi + k, st))) return rc;
@@ -617,6 +621,15 @@ int mmg_get_params(const mmg_map* m, mmg_params* p)
     if (!m || !p) return MMG_ERR_INVALID_ARG;
     *p = m->prm;
     return MMG_OK;
+}
+
+int mmg_reserve(mmg_map* m, uint64_t voxels)
+{
+    MMG_CHECK_MAP(m);
+    if (m->kind == MMG_SPARSE_TREES) return MMG_OK;  // blocks grow on demand
+    int rc = ensure_table(m, voxels, 0);
+    if (!rc) rc = ensure_rows(m, voxels, 0);
+    return rc;
 }
 
 int mmg_insert_batch(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, int has_robot_pose, int mem,

@@ -129,6 +129,8 @@ __global__ void __launch_bounds__(256)
         ok = Tr::to_index(g.x, inv, cx) & Tr::to_index(g.y, inv, cy) & Tr::to_index(g.z, inv, cz);
         if (!ok) atomicAdd(&m.ctr->oob, 1u);
     }
+    // before the probes: every warp reaches the barrier inside at once (after them it would wait for the slowest prober)
+    if (bbox_all) block_bbox_atomics(m.ctr, ok, g.x, g.y, g.z, sm_bbox);
     const int lane   = lane_id();
     const u64 key    = ok ? pack_key(cx, cy, cz) : (KEY_EMPTY - 1 - (u64)lane);  // invalid lanes never match each other
     const u32 peers  = __match_any_sync(MMG_FULL, key);
@@ -157,7 +159,6 @@ __global__ void __launch_bounds__(256)
             }
         }
     }
-    if (bbox_all) block_bbox_atomics(m.ctr, ok, g.x, g.y, g.z, sm_bbox);
 }
 
 template <class Tr>

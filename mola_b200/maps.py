@@ -133,6 +133,10 @@ class _Map:
         capi.check(rc, allow=(capi.MMG_ERR_OUT_OF_RANGE,))
         return rc == capi.MMG_ERR_OUT_OF_RANGE
 
+    def reserve(self, voxels):
+        """voxels_.reserve(): pre-sizes the table and the row store (HashedVoxelPointCloud.cpp:1070)."""
+        capi.check(self._lib.mmg_reserve(self._h, C.c_uint64(int(voxels))))
+
     def insertPointClouds(self, xs, ys, zs, scan_offsets, robotPoses, with_eviction=True):
         """A sequence of insertObservation calls in one batch: scan s is points
         [scan_offsets[s], scan_offsets[s+1]) with pose robotPoses[s] (12 doubles each). Same result as
