@@ -147,6 +147,17 @@ int mmg_nn_radius_batch(mmg_map* m, const float* xs, const float* ys, const floa
 int mmg_nn_radius_fetch(mmg_map* m, float* out_xyz, float* out_d2, uint64_t* out_id, int mem,
                         void* stream);
 
+/* Batched point matcher: what mp2p_icp's Matcher_Points_DistanceThreshold does with one
+ * nn_single_search call per scan point (the reference's NearestNeighborsCapable contract,
+ * include/mola_metric_maps/HashedVoxelPointCloud.h:303-332) as ONE device pass: compose each local point
+ * with pose12, nearest map point, keep the pair iff found and d2 < max_dist_sqr (strict), and write the
+ * pairings compacted in local-point order. Output arrays are sized for n pairings; *out_count (host)
+ * receives the number written. The threshold doubles as the initial search radius of the kernel. */
+int mmg_match_batch(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n,
+                    const double* pose12, float max_dist_sqr, uint64_t* out_count,
+                    uint32_t* out_local_idx, float* out_xyz /*map point*/, float* out_d2, uint64_t* out_id,
+                    int mem, void* stream);
+
 /* log-likelihood of a scan, see reference :509-546. */
 int mmg_likelihood(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n,
                    const double* pose12, double* out_loglik, int mem, void* stream);

@@ -345,19 +345,19 @@ struct OutBufs
 
 template <class Tr>
 static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy, const float* dz, size_t nq, size_t stride, const PoseD& T, int use_pose,
-                             const QueryOut& o, cudaStream_t st)
+                             const QueryOut& o, cudaStream_t st, float bd_init = INFINITY)
 {
     // A/B switch for the profiles: MMG_NN_KERNEL = pruned (default) | grouped | simple
     static const int variant = [] {
         const char* e = getenv("MMG_NN_KERNEL");
         return !e ? 0 : (!strcmp(e, "grouped") ? 1 : (!strcmp(e, "simple") ? 2 : 0));
     }();
-    if (variant == 2)
+    if (variant == 2 && bd_init == INFINITY)
     {
         const unsigned nb = persistent_blocks(m, nq, 8, 8);
         MMG_LAUNCH((k_nn_single<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, o);
     }
-    else if (variant == 1)
+    else if (variant == 1 && bd_init == INFINITY)
     {
         const unsigned nb = persistent_blocks(m, (nq + 31) / 32, 8, 8);
         MMG_LAUNCH((k_nn_single_grouped<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o);
@@ -365,13 +365,13 @@ static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy,
     else
     {
         const unsigned nb = (unsigned)std::min<size_t>((nq + 255) / 256, (size_t)m->num_sms * 64);
-        MMG_LAUNCH((k_nn_single_pruned<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o);
+        MMG_LAUNCH((k_nn_single_pruned<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);
     }
 }
 
 template <class Tr>
 static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, size_t stride, const double* pose12,
-                           uint8_t* ofound, float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st)
+                           uint8_t* ofound, float* oxyz, float* od2, uint64_t* oid, int mem, cudaStream_t st, float bd_init = INFINITY)
 {
     mmg_map* m = const_cast<mmg_map*>(cm);
     if (n == 0) return MMG_OK;
@@ -379,7 +379,7 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
     const PoseD  T  = make_pose(pose12);
     if (mem == MMG_MEM_DEVICE)
     {
-        launch_nn_single<Tr>(m, xs, ys, zs, nq, stride, T, pose12 ? 1 : 0, QueryOut{ofound, oxyz, od2, (u64*)oid}, st);
+        launch_nn_single<Tr>(m, xs, ys, zs, nq, stride, T, pose12 ? 1 : 0, QueryOut{ofound, oxyz, od2, (u64*)oid}, st, bd_init);
         MMG_CUDA(cudaGetLastError());
         return MMG_OK;
     }
@@ -448,7 +448,7 @@ static int nn_multi_voxel(const mmg_map* cm, const float* xs, const float* ys, c
         did = (u64*)ob, dxyz = (float*)(ob + n * k * 8), dd2 = (float*)(ob + n * k * 20), dc = (u32*)(ob + n * k * 24);
     }
     const PoseD T = make_pose(pose12);
-    MMG_LAUNCH((k_nn_multi<Tr, K, REF>), (unsigned)((n + 127) / 128), 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, (u32)k, dc, dxyz,
+    MMG_LAUNCH((k_nn_multi<Tr, K, REF>), (unsigned)((n + 127) / 128), 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, m->prm.voxel_size, (u32)k, dc, dxyz,
                dd2, did);
     MMG_CUDA(cudaGetLastError());
     if (mem == MMG_MEM_HOST)
@@ -476,7 +476,7 @@ static int radius_hashed(mmg_map* m, const float* xs, const float* ys, const flo
     const float r = r2 > 0 ? std::sqrt(r2) : 0.f;
     const u32   mp = (u32)std::min<size_t>(maxp, 0xFFFFFFFFu);
     const unsigned g = (unsigned)((n + 127) / 128);
-    MMG_LAUNCH((k_radius_hashed<Tr, 0>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, r2, r, mp, counts, (const u64*)nullptr,
+    MMG_LAUNCH((k_radius_hashed<Tr, 0>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, m->prm.voxel_size, r2, r, mp, counts, (const u64*)nullptr,
                (float*)nullptr, (float*)nullptr, (u64*)nullptr);
     exclusive_scan<u32, u64>(counts, offs, n, offs + n, offs + n + 1, st);
     u64 total = 0;
@@ -487,7 +487,7 @@ static int radius_hashed(mmg_map* m, const float* xs, const float* ys, const flo
     if (!hb) return MMG_ERR_OUT_OF_MEM;
     m->rad_id = (u64*)hb, m->rad_xyz = (float*)(hb + total * 8), m->rad_d2 = (float*)(hb + total * 20);
     if (total)
-        MMG_LAUNCH((k_radius_hashed<Tr, 1>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, r2, r, mp, counts, offs, m->rad_xyz,
+        MMG_LAUNCH((k_radius_hashed<Tr, 1>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, m->prm.voxel_size, r2, r, mp, counts, offs, m->rad_xyz,
                    m->rad_d2, m->rad_id);
     MMG_CUDA(cudaGetLastError());
     if (mem == MMG_MEM_HOST)
@@ -507,6 +507,87 @@ static int radius_hashed(mmg_map* m, const float* xs, const float* ys, const flo
         return MMG_ERR_INVALID_ARG;               \
     }                                             \
     MMG_CUDA(cudaSetDevice((m)->device))
+
+// ------------------------------------------------------------------ matcher
+static __global__ void k_match_threshold(uint8_t* __restrict__ found, const float* __restrict__ d2, u32 n, float max_d2)
+{
+    const u32 q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < n && found[q] && !(d2[q] < max_d2)) found[q] = 0;
+}
+static __global__ void k_match_scatter(const uint8_t* __restrict__ found, const u32* __restrict__ offs, u32 n, const float* __restrict__ xyz,
+                                       const float* __restrict__ d2, const u64* __restrict__ id, u32* __restrict__ oidx, float* __restrict__ oxyz,
+                                       float* __restrict__ od2, u64* __restrict__ oid)
+{
+    const u32 q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n || !found[q]) return;
+    const size_t o = offs[q];
+    oidx[o]        = q;
+    oxyz[3 * o] = xyz[3 * (size_t)q], oxyz[3 * o + 1] = xyz[3 * (size_t)q + 1], oxyz[3 * o + 2] = xyz[3 * (size_t)q + 2];
+    od2[o] = d2[q];
+    oid[o] = id[q];
+}
+
+extern "C" int mmg_match_batch(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12,
+                               float max_dist_sqr, uint64_t* out_count, uint32_t* out_local_idx, float* out_xyz, float* out_d2, uint64_t* out_id,
+                               int mem, void* stream)
+{
+    MMG_CHECK_MAP(cm);
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (!out_count || (n && (!xs || !ys || !zs || !out_local_idx || !out_xyz || !out_d2 || !out_id)) || n >= (1ull << 31)) return MMG_ERR_INVALID_ARG;
+    *out_count = 0;
+    if (n == 0) return MMG_OK;
+    if (m->kind == MMG_SPARSE_VOXEL)
+    {  // the matcher calls nn_single_search, which throws for this map type (SparseVoxelPointCloud.cpp:695-719)
+        set_error("n-search not available in this map type");
+        return MMG_ERR_UNSUPPORTED;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const float *dx, *dy, *dz;
+    int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
+    if (rc) return rc;
+    // dense nn_single results + scan scratch + (host callers) the compacted outputs
+    const size_t dense = n * 32, scanb = (n + 2 + scan_scratch_elems(n)) * sizeof(u32), comp = mem == MMG_MEM_HOST ? n * 28 : 0;
+    char*        ob    = (char*)m->scratch_get(S_MATCH, dense + scanb + comp + 256);
+    if (!ob) return MMG_ERR_OUT_OF_MEM;
+    u64*     id   = (u64*)ob;
+    float*   xyz  = (float*)(ob + n * 8);
+    float*   d2   = (float*)(ob + n * 20);
+    uint8_t* fnd  = (uint8_t*)(ob + n * 24);
+    u32*     offs = (u32*)(ob + ((dense + 63) / 64) * 64);
+    char*    cb   = (char*)offs + ((scanb + 63) / 64) * 64;
+    if (m->kind == MMG_HASHED_VOXEL)
+    {
+        // "d2 < max" as the initial search radius: the largest float below max (nothing when max <= 0)
+        const float bd = std::isinf(max_dist_sqr) && max_dist_sqr > 0 ? INFINITY : std::nextafterf(max_dist_sqr, -INFINITY);
+        rc             = nn_single_voxel<HashedTraits>(m, dx, dy, dz, n, 1, pose12, fnd, xyz, d2, (uint64_t*)id, MMG_MEM_DEVICE, st, bd);
+    }
+    else
+    {
+        rc = trees_nn_single(m, dx, dy, dz, n, 1, pose12, fnd, xyz, d2, (uint64_t*)id, MMG_MEM_DEVICE, st);
+        if (!rc) MMG_LAUNCH(k_match_threshold, (unsigned)((n + 255) / 256), 256, 0, st, fnd, d2, (u32)n, max_dist_sqr);
+    }
+    if (rc) return rc;
+    exclusive_scan<uint8_t, u32>(fnd, offs, n, offs + n, offs + n + 1, st);
+    u32*   oi = out_local_idx;
+    float *ox = out_xyz, *od = out_d2;
+    u64*   oid = (u64*)out_id;
+    if (mem == MMG_MEM_HOST) oid = (u64*)cb, ox = (float*)(cb + n * 8), od = (float*)(cb + n * 20), oi = (u32*)(cb + n * 24);
+    MMG_LAUNCH(k_match_scatter, (unsigned)((n + 255) / 256), 256, 0, st, fnd, offs, (u32)n, xyz, d2, id, oi, ox, od, oid);
+    MMG_CUDA(cudaGetLastError());
+    u32 total = 0;
+    MMG_CUDA(cudaMemcpyAsync(&total, offs + n, sizeof(u32), cudaMemcpyDeviceToHost, st));
+    MMG_CUDA(cudaStreamSynchronize(st));
+    *out_count = total;
+    if (mem == MMG_MEM_HOST && total)
+    {
+        MMG_CUDA(cudaMemcpyAsync(out_id, oid, (size_t)total * 8, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(out_xyz, ox, (size_t)total * 12, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(out_d2, od, (size_t)total * 4, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(out_local_idx, oi, (size_t)total * 4, cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaStreamSynchronize(st));
+    }
+    return MMG_OK;
+}
 
 extern "C" {
 

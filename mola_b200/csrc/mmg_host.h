@@ -39,6 +39,7 @@ enum ScratchSlot
     S_QID,
     S_LIK,
     S_SCANS,
+    S_MATCH,
     S_TREES0,
     S_TREES1,
     S_TREES2,

@@ -235,8 +235,10 @@ __device__ __forceinline__ void nn_visit_cell(const VoxelMapDev& m, int b, int c
 template <class Tr>
 __global__ void __launch_bounds__(256)
     k_nn_single_pruned(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride,
-                       PoseD pose, int use_pose, float inv, float vsize, QueryOut out)
+                       PoseD pose, int use_pose, float inv, float vsize, QueryOut out, float bd_init)
 {
+    // bd_init = +inf for nn_single_search; the matcher passes the largest float below its squared distance
+    // threshold, which turns "d2 < threshold" into the initial branch-and-bound radius (mmg_match_batch)
     constexpr int CAP = Tr::CAP;
     for (u32 q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x)
     {
@@ -245,7 +247,7 @@ __global__ void __launch_bounds__(256)
         if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
         int        cx, cy, cz;
         const bool ok = Tr::to_index(p.x, inv, cx) & Tr::to_index(p.y, inv, cy) & Tr::to_index(p.z, inv, cz);
-        float      bd = __int_as_float(0x7f800000);
+        float      bd = bd_init;
         u32        br = 0xFFFFFFFFu, bv = 0;
         if (ok)
         {

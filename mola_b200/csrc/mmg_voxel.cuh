@@ -526,6 +526,45 @@ __device__ __forceinline__ void visit_cells(const VoxelMapDev& m, int ax, int ay
             }
 }
 
+// Conservative squared distance from coordinate q to the slab of cell index c along one axis (the cell's
+// coordinate span widened by a few ulps and the square scaled down, like voxel_lower_bound()).
+template <class Tr>
+__device__ __forceinline__ float axis_gap(int c, float vsize, float q)
+{
+    float lo, hi;
+    Tr::cell_span(c, lo, hi);
+    const float eps = (fabsf((float)c) + 2.0f) * vsize * 1e-6f;
+    const float d   = fmaxf(0.f, fmaxf(lo * vsize - eps - q, q - (hi * vsize + eps)));
+    return d * d * 0.9999f;
+}
+
+// visit_cells in the same (reference) order, but a cell is skipped, before its hash probe, when its box lies
+// farther from p than bound(): exact as long as every candidate with d2 > bound() is a no-op for f at that moment.
+template <class Tr, class B, class F>
+__device__ __forceinline__ void visit_cells_bounded(const VoxelMapDev& m, int ax, int ay, int az, int bx, int by, int bz, const float3& p, float vsize,
+                                                    B&& bound, F&& f)
+{
+    constexpr int CAP = Tr::CAP;
+    for (int x = ax; x <= bx; x++)
+    {
+        const float gx = axis_gap<Tr>(x, vsize, p.x);
+        if (gx > bound()) continue;
+        for (int y = ay; y <= by; y++)
+        {
+            const float gxy = gx + axis_gap<Tr>(y, vsize, p.y);
+            if (gxy > bound()) continue;
+            for (int z = az; z <= bz; z++)
+            {
+                if (gxy + axis_gap<Tr>(z, vsize, p.z) > bound()) continue;
+                if (!index_in_range(x, y, z)) continue;
+                u32 vid, cnt;
+                if (!probe_ro(m.table, m.mask, pack_key(x, y, z), vid, cnt)) continue;
+                for (u32 s = 0; s < cnt; s++) f(x, y, z, (int)s, vid, __ldg(&m.pts[(size_t)vid * CAP + s]));
+            }
+        }
+    }
+}
+
 struct Hit3
 {
     float x, y, z, d2;
@@ -557,7 +596,8 @@ struct Slots
 template <class Tr, int K, bool REF_SHIFT>
 __global__ void __launch_bounds__(128)
     k_nn_multi(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, PoseD pose,
-               int use_pose, float inv, u32 kreq, u32* __restrict__ ocount, float* __restrict__ oxyz, float* __restrict__ od2, u64* __restrict__ oid)
+               int use_pose, float inv, float vsize, u32 kreq, u32* __restrict__ ocount, float* __restrict__ oxyz, float* __restrict__ od2,
+               u64* __restrict__ oid)
 {
     const u32 q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
@@ -566,10 +606,16 @@ __global__ void __launch_bounds__(128)
     int cx, cy, cz;
     const bool ok = Tr::to_index(p.x, inv, cx) & Tr::to_index(p.y, inv, cy) & Tr::to_index(p.z, inv, cz);
     Slots<K, REF_SHIFT> s;
+    // Reference visiting order (the K=3 shift defect makes the third slot order dependent). A candidate that is
+    // not strictly below the current last slot leaves the slots untouched (offer() walks past all K), and slot values never
+    // grow, so once K slots are filled any cell whose box is farther than slot K-1 can be skipped without changing anything.
     if (ok)
-        visit_cells<Tr>(m, cx - 1, cy - 1, cz - 1, cx + 1, cy + 1, cz + 1, [&](int x, int y, int z, int slot, u32, const float4& t) {
-            s.offer(sqr_dist(t.x, t.y, t.z, p.x, p.y, p.z), t.x, t.y, t.z, plain_id<Tr::SLOT_BITS>(x, y, z, slot));
-        });
+        visit_cells_bounded<Tr>(
+            m, cx - 1, cy - 1, cz - 1, cx + 1, cy + 1, cz + 1, p, vsize,
+            [&]() { return s.found == K ? s.m[K - 1].d2 : __int_as_float(0x7f800000); },
+            [&](int x, int y, int z, int slot, u32, const float4& t) {
+                s.offer(sqr_dist(t.x, t.y, t.z, p.x, p.y, p.z), t.x, t.y, t.z, plain_id<Tr::SLOT_BITS>(x, y, z, slot));
+            });
     const u32 nout = min(kreq, (u32)s.found);
     ocount[q]      = nout;
     for (u32 i = 0; i < nout; i++)
@@ -585,7 +631,7 @@ __global__ void __launch_bounds__(128)
 template <class Tr, int PASS>
 __global__ void __launch_bounds__(128)
     k_radius_hashed(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, PoseD pose,
-                    int use_pose, float inv, float r2, float r, u32 maxp, u32* __restrict__ counts, const u64* __restrict__ offsets,
+                    int use_pose, float inv, float vsize, float r2, float r, u32 maxp, u32* __restrict__ counts, const u64* __restrict__ offsets,
                     float* __restrict__ oxyz, float* __restrict__ od2, u64* __restrict__ oid)
 {
     const u32 q = blockIdx.x * blockDim.x + threadIdx.x;
@@ -598,8 +644,10 @@ __global__ void __launch_bounds__(128)
     u32  c = 0;
     u64  o = PASS ? offsets[q] : 0;
     Slots<3, true> s;
+    // cells of the reference's index box that lie wholly outside the sphere hold only d > r2 candidates, which the
+    // reference drops (:832): skipping them changes nothing
     if (ok && r2 > 0.f)
-        visit_cells<Tr>(m, a[0], a[1], a[2], b[0], b[1], b[2], [&](int x, int y, int z, int slot, u32, const float4& t) {
+        visit_cells_bounded<Tr>(m, a[0], a[1], a[2], b[0], b[1], b[2], p, vsize, [&]() { return r2; }, [&](int x, int y, int z, int slot, u32, const float4& t) {
             const float d = sqr_dist(t.x, t.y, t.z, p.x, p.y, p.z);
             if (d > r2) return;
             if (maxp != 0) { s.offer(d, t.x, t.y, t.z, plain_id<Tr::SLOT_BITS>(x, y, z, slot)); return; }

@@ -241,6 +241,24 @@ class _Map:
         self._raise_like_reference(rc)
         return found, pts, d2, ids
 
+    def match_points_batch(self, xs, ys, zs, pose=None, max_dist_sqr=float("inf")):
+        """Batched distance-threshold matcher (what mp2p_icp's Matcher_Points_DistanceThreshold does with one
+        nn_single_search per point): returns (local_idx[m] uint32, map_pts[m,3], d2[m], ids[m]) for the points
+        whose nearest map point lies at d2 < max_dist_sqr, in local-point order."""
+        self._sync_params()
+        mem, st, keep, px, py, pz, n, th = self._xyz(xs, ys, zs)
+        idx = self._alloc(th, (n,), np.uint32, "int32")
+        pts = self._alloc(th, (n, 3), np.float32, "float32")
+        d2 = self._alloc(th, (n,), np.float32, "float32")
+        ids = self._alloc(th, (n,), np.uint64, "int64")
+        cnt = C.c_uint64()
+        pk, pp = capi.pose_ptr(pose)
+        rc = self._lib.mmg_match_batch(self._h, px, py, pz, C.c_size_t(n), pp, C.c_float(max_dist_sqr), C.byref(cnt), self._ptr(idx),
+                                       self._ptr(pts), self._ptr(d2), self._ptr(ids), mem, st)
+        self._raise_like_reference(rc)
+        m = int(cnt.value)
+        return idx[:m], pts[:m], d2[:m], ids[:m]
+
     def nn_multiple_search_batch(self, xs, ys, zs, N, pose=None):
         """Batched nn_multiple_search. Returns (count[n], pts[n,N,3], d2[n,N], ids[n,N])."""
         if N <= 0:

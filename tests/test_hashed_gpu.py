@@ -267,3 +267,31 @@ def test_insert_adversarial_order(built):
         g.insertPointCloud(x, y, z)
         o.insert(x, y, z)
         assert_same_map(g, o)
+
+
+@pytest.mark.parametrize("thr", [0.05, 0.2, 0.75, float("inf"), 0.0])
+def test_match_points_batch(built, thr):
+    """Matcher = nn_single_search per point + 'd2 < thr^2' filter + order-preserving compaction
+    (oracle: the reference's nn_single_search restated, filtered in numpy)."""
+    from mola_b200 import synth
+    g, o = _maps(0.5)
+    xs, ys, zs, pose = _scan()
+    g.insertPointCloud(xs, ys, zs, pose)
+    o.insert(xs, ys, zs, pose)
+    qpose = synth.perturbed_pose(pose, dx=0.15, dyaw_deg=0.8)
+    qx, qy, qz = compose_host(qpose, xs, ys, zs)
+    of, op, od, oi = o.nn_single(qx, qy, qz)
+    t2 = np.float32(thr) * np.float32(thr)
+    keep = (of > 0) & (od < t2)
+    idx, pts, d2, ids = g.match_points_batch(xs, ys, zs, pose=qpose, max_dist_sqr=float(t2))
+    assert np.array_equal(idx, np.nonzero(keep)[0].astype(np.uint32))
+    assert np.array_equal(ids, oi[keep])
+    assert np.array_equal(d2.view(np.uint32), od[keep].view(np.uint32))
+    assert np.array_equal(pts.view(np.uint32), op[keep].view(np.uint32))
+    if 0 < thr < 1:
+        assert 0 < idx.size < xs.size
+    # device buffers give the same pairings
+    import torch
+    d = [torch.from_numpy(a).cuda() for a in (xs, ys, zs)]
+    idx2, pts2, d22, ids2 = g.match_points_batch(d[0], d[1], d[2], pose=qpose, max_dist_sqr=float(t2))
+    assert np.array_equal(idx2.cpu().numpy().view(np.uint32), idx) and np.array_equal(ids2.cpu().numpy().view(np.uint64), ids)

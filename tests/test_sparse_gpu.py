@@ -192,3 +192,18 @@ def test_sparse_trees_insert_scans_falls_back(built):
     for s in scans:
         o.insert(*s)
     _same_export(g, o)
+
+
+def test_sparse_trees_match_points(built):
+    g, o = _pair(2, 10.0, minimum_points_clearance=0.05)
+    sc = _scan("tiny")
+    g.insert(*sc)
+    o.insert(*sc)
+    q = compose_host(sc[3], sc[0] + np.float32(0.04), sc[1], sc[2])
+    of, op, od, oi = o.nn_single(*q)
+    t2 = np.float32(np.median(od[of > 0]))  # a threshold that some pairs reach exactly: '<' is strict
+    keep = (of > 0) & (od < t2)
+    idx, pts, d2, ids = g.m.match_points_batch(*q, max_dist_sqr=float(t2))
+    assert 0 < idx.size < q[0].size
+    assert np.array_equal(idx, np.nonzero(keep)[0].astype(np.uint32)) and np.array_equal(ids, oi[keep])
+    assert np.array_equal(bits(d2), bits(od[keep])) and np.array_equal(bits(pts), bits(op[keep]))
