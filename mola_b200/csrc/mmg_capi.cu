@@ -364,8 +364,13 @@ static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy,
     }
     else
     {
-        const unsigned nb = (unsigned)std::min<size_t>((nq + 255) / 256, (size_t)m->num_sms * 64);
-        MMG_LAUNCH((k_nn_single_pruned<Tr>), nb, 256, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);
+        static const unsigned bs = [] {  // block size, tunable for the profiles (MMG_NN_BLOCK = 64 | 128 | 256)
+            const char* e = getenv("MMG_NN_BLOCK");
+            const int   v = e ? atoi(e) : 0;
+            return (unsigned)((v == 64 || v == 128 || v == 256) ? v : 256);
+        }();
+        const unsigned nb = (unsigned)std::min<size_t>((nq + bs - 1) / bs, (size_t)m->num_sms * 64 * (256 / bs));
+        MMG_LAUNCH((k_nn_single_pruned<Tr>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);
     }
 }
 
@@ -383,7 +388,31 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
         MMG_CUDA(cudaGetLastError());
         return MMG_OK;
     }
-    // Host buffers: the batch is cut into up to 8 chunks and the three stages run on three streams,
+    // Pinned (page-locked, mapped) host buffers: ONE launch reads the queries and writes the results straight over PCIe
+    // (coalesced loads / whole-line stores, both directions busy at once, no staging copies, no per-chunk copy calls).
+    static const bool no_zero_copy = getenv("MMG_E2E_PIPELINE") != nullptr;  // A/B switch for the profiles
+    if (stride == 1 && !no_zero_copy)
+    {
+        const void* hp[7] = {xs, ys, zs, ofound, oxyz, od2, oid};
+        void*       dp[7];
+        bool        all = true;
+        for (int i = 0; i < 7 && all; i++)
+        {
+            cudaPointerAttributes at;
+            all = cudaPointerGetAttributes(&at, hp[i]) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer != nullptr;
+            dp[i] = all ? at.devicePointer : nullptr;
+        }
+        cudaGetLastError();
+        if (all)
+        {
+            launch_nn_single<Tr>(m, (const float*)dp[0], (const float*)dp[1], (const float*)dp[2], nq, 1, T, pose12 ? 1 : 0,
+                                 QueryOut{(uint8_t*)dp[3], (float*)dp[4], (float*)dp[5], (u64*)dp[6]}, st, bd_init);
+            MMG_CUDA(cudaGetLastError());
+            MMG_CUDA(cudaStreamSynchronize(st));
+            return MMG_OK;
+        }
+    }
+    // Pageable host buffers: the batch is cut into up to 8 chunks and the three stages run on three streams,
     // so the H2D copy of chunk c+1, the kernel of chunk c and the D2H copy of chunk c-1 overlap
     // (PCIe is full duplex; the kernel is far shorter than either copy).
     if (stride != 1)

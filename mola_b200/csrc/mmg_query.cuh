@@ -239,16 +239,25 @@ __global__ void __launch_bounds__(256)
 {
     // bd_init = +inf for nn_single_search; the matcher passes the largest float below its squared distance
     // threshold, which turns "d2 < threshold" into the initial branch-and-bound radius (mmg_match_batch)
-    constexpr int CAP = Tr::CAP;
-    for (u32 q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x)
+    constexpr int CAP  = Tr::CAP;
+    const int     lane = lane_id();
+    // warp-uniform trip count: the coalesced result stores below shuffle across the whole warp
+    for (u32 q0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); q0 < n; q0 += gridDim.x * blockDim.x)
     {
-        const size_t qi = (size_t)q * stride;
-        float3       p  = make_float3(qx[qi], qy[qi], qz[qi]);
-        if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
-        int        cx, cy, cz;
-        const bool ok = Tr::to_index(p.x, inv, cx) & Tr::to_index(p.y, inv, cy) & Tr::to_index(p.z, inv, cz);
-        float      bd = bd_init;
-        u32        br = 0xFFFFFFFFu, bv = 0;
+        const u32  q     = q0 + (u32)lane;
+        const bool valid = q < n;
+        float3     p     = make_float3(0.f, 0.f, 0.f);
+        int        cx = 0, cy = 0, cz = 0;
+        bool       ok = false;
+        if (valid)
+        {
+            const size_t qi = (size_t)q * stride;
+            p               = make_float3(qx[qi], qy[qi], qz[qi]);
+            if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
+            ok = Tr::to_index(p.x, inv, cx) & Tr::to_index(p.y, inv, cy) & Tr::to_index(p.z, inv, cz);
+        }
+        float bd = bd_init;
+        u32   br = 0xFFFFFFFFu, bv = 0;
         if (ok)
         {
             float gx[3], gy[3], gz[3];
@@ -282,10 +291,21 @@ __global__ void __launch_bounds__(256)
             t  = __ldg(m.pts + (size_t)bv * CAP + slot);
             id = plain_id<Tr::SLOT_BITS>(cx + b / 9 - 1, cy + (b / 3) % 3 - 1, cz + b % 3 - 1, slot);
         }
-        out.found[q]           = found ? 1 : 0;
-        out.xyz[3 * (size_t)q] = t.x, out.xyz[3 * (size_t)q + 1] = t.y, out.xyz[3 * (size_t)q + 2] = t.z;
-        out.d2[q] = found ? bd : 0.f;
-        out.id[q] = id;
+        if (valid)
+        {
+            out.found[q] = found ? 1 : 0;
+            out.d2[q]    = found ? bd : 0.f;
+            out.id[q]    = id;
+        }
+        // xyz is an array of structs: transpose through shuffles so the warp writes its 96 floats as three fully
+        // coalesced 128-byte stores (matters most when `out` is mapped host memory: whole PCIe write bursts)
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+        {
+            const int   w = 32 * k + lane, src = w / 3, c = w - 3 * src;
+            const float vx = __shfl_sync(MMG_FULL, t.x, src), vy = __shfl_sync(MMG_FULL, t.y, src), vz = __shfl_sync(MMG_FULL, t.z, src);
+            if (q0 + (u32)src < n) out.xyz[3 * (size_t)q0 + w] = c == 0 ? vx : (c == 1 ? vy : vz);
+        }
     }
 }
 }  // namespace mmg

@@ -45,6 +45,9 @@ int mmo_insert(void* h, const float* xs, const float* ys, const float* zs, size_
  * nthreads>1 shards the (const) query batch over std::threads. */
 int mmo_nn_single(void* h, const float* xs, const float* ys, const float* zs, size_t n,
                   uint8_t* found, float* out_xyz, float* out_d2, uint64_t* out_id, int nthreads);
+/* Port only: SparseVoxel k-NN, which the reference throws for, answers with the k <= 8 smallest
+ * (d2, scan order) of the 27-cell stencil. Checker for the extension; off by default. */
+int mmo_enable_knn_extension(void* h, int on);
 int mmo_nn_multi(void* h, const float* xs, const float* ys, const float* zs, size_t n, size_t k,
                  uint32_t* out_count, float* out_xyz, float* out_d2, uint64_t* out_id,
                  int nthreads);

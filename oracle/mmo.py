@@ -85,6 +85,11 @@ class OracleMap:
     def clear(self):
         self.lib.mmo_clear(self.h)
 
+    def enable_knn_extension(self, on=True):
+        """Port only: SparseVoxel k-NN (extension N4) instead of the reference's throw."""
+        if self.lib.mmo_enable_knn_extension(self.h, 1 if on else 0):
+            raise RuntimeError("the k-NN extension exists for the SparseVoxel port only")
+
     def isEmpty(self):
         return bool(self.lib.mmo_is_empty(self.h))
 

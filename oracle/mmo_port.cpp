@@ -405,8 +405,46 @@ struct SparseVoxel : MapBase
     {  // internal_insertObservation: no eviction in this map type, SparseVoxelPointCloud.cpp:362-380
         for (size_t i = 0; i < n; i++) insert_point(compose(T, xs[i], ys[i], zs[i]));
     }
-    int nn_single_one(const P3&, Hit&, bool&) const override { return -5; }      // throws, :695-719
-    int nn_multi_one(const P3&, size_t, Hit*, size_t&) const override { return -5; }
+    // The reference throws here (:695-719). With knn_ext set (test/bench infrastructure for the extension of
+    // SURVEY N4) the port answers instead: the k <= 8 lexicographically smallest (d2, scan order) over the
+    // 27-cell stencil of round-based indices, cells visited cx, cy, cz ascending, slots ascending.
+    bool knn_ext = false;
+    int  nn_single_one(const P3& q, Hit& out, bool& found) const override
+    {
+        if (!knn_ext) return -5;
+        size_t n = 0;
+        nn_multi_one(q, 1, &out, n);
+        found = n > 0;
+        return 0;
+    }
+    int nn_multi_one(const P3& q, size_t k, Hit* out, size_t& nout) const override
+    {
+        if (!knn_ext) return -5;
+        if (k > 8) return -5;
+        const Key c = to_idx(q);
+        nout        = 0;
+        for (int x = c.cx - 1; x <= c.cx + 1; x++)
+            for (int y = c.cy - 1; y <= c.cy + 1; y++)
+                for (int z = c.cz - 1; z <= c.cz + 1; z++)
+                {
+                    auto it = vox.find(Key{x, y, z});
+                    if (it == vox.end()) continue;
+                    for (int s = 0; s < it->second.n; s++)
+                    {
+                        const P3&   p  = it->second.pts[s];
+                        const float dx = p.x - q.x, dy = p.y - q.y, dz = p.z - q.z;
+                        const float d2 = (dx * dx + dy * dy) + dz * dz;
+                        size_t      i  = 0;
+                        while (i < nout && !(d2 < out[i].d2)) i++;  // strict '<': the first seen wins ties
+                        if (i >= k) continue;
+                        const size_t last = std::min(nout + 1, k);
+                        for (size_t j = last - 1; j > i; j--) out[j] = out[j - 1];
+                        out[i] = {p, d2, plain_id(Key{x, y, z}, s)};
+                        if (nout < k) nout++;
+                    }
+                }
+        return 0;
+    }
     int radius_one(const P3& q, float r2, size_t maxp, std::vector<Hit>& out) const override
     {  // nn_radius_search, SparseVoxelPointCloud.cpp:721-798
         if (r2 <= 0) return 0;
@@ -758,6 +796,13 @@ int mmo_nn_single(void* h, const float* xs, const float* ys, const float* zs, si
         }
     });
     return rc;
+}
+int mmo_enable_knn_extension(void* h, int on)
+{
+    auto* sv = dynamic_cast<SparseVoxel*>((MapBase*)h);
+    if (!sv) return -5;
+    sv->knn_ext = on != 0;
+    return 0;
 }
 int mmo_nn_multi(void* h, const float* xs, const float* ys, const float* zs, size_t n, size_t k,
                  uint32_t* ocount, float* oxyz, float* od2, uint64_t* oid, int nthreads)

@@ -89,6 +89,12 @@ def test_sparse_voxel_c3_knn_extension(built):
         k = min(8, len(cand))
         assert cnt[j] == k
         assert np.array_equal(d2[j, :k], np.array([c_[0] for c_ in cand[:k]], np.float32))
+    # the C++ port's extension mode (what bench_configs.py times) agrees on every query, ids included
+    o.enable_knn_extension()
+    oc, op, od, oi = o.nn_multi(*q, 8)
+    mk = np.arange(8)[None, :] < oc[:, None]
+    assert np.array_equal(cnt, oc) and np.array_equal(ids[mk], oi[mk]) and np.array_equal(bits(d2[mk]), bits(od[mk]))
+    assert np.array_equal(bits(pts[mk]), bits(op[mk]))
 
 
 @pytest.mark.parametrize("opts", [dict(), dict(minimum_points_clearance=0.5), dict(minimum_points_clearance=0.05, remove_voxels_farther_than=25.0)])
