@@ -107,6 +107,29 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Pins this process to the CPUs next to its GPU (sysfs local_cpulist of the GPU's PCI function) before any pinned
+    buffer is allocated, so the host side of the e2e copies stays on the GPU's NUMA node. torchrun does not bind ranks.
+    Returns the cpulist string, or None when the topology cannot be read (nothing is changed then)."""
+    try:
+        out = subprocess.run(["nvidia-smi", f"--id={local_rank}", "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                             capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        bus = out[-12:] if len(out) >= 12 else out          # 00000000:1B:00.0 -> 0000:1b:00.0
+        path = f"/sys/bus/pci/devices/{bus}/local_cpulist"
+        cl = open(path).read().strip()
+        cpus = set()
+        for part in cl.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= set(os.sched_getaffinity(0))
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cl
+    except Exception:
+        return None
+
+
 def cpu_threads():
     return max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
 
@@ -213,6 +236,7 @@ def run_gpu(args, rank, world, local_rank):
     from mola_b200.maps import Communicator
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     log = (lambda s: print(s, file=sys.stderr, flush=True)) if (args.verbose and rank == 0) else None
     lib = capi.lib()
     t_setup = time.perf_counter()
@@ -358,7 +382,7 @@ def run_gpu(args, rank, world, local_rank):
             "config": {"workload": "C2: 10M-pt HashedVoxelPointCloud (voxel 0.5 m), batched nn_single_search of 1M points per step per GPU",
                        "map_points": int(stats["points"]), "map_voxels": int(stats["live_voxels"]), "map_scans": nscans,
                        "queries_per_step_per_gpu": n, "l2": "flushed between steps (256 MiB write)", "map_hbm_bytes": int(stats["hbm_bytes"]),
-                       "parallelism": f"map replicated by NCCL broadcast, queries sharded x{world}"},
+                       "parallelism": f"map replicated by NCCL broadcast, queries sharded x{world}", "rank0_cpu_binding": numa},
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": 12 * n, "d2h_bytes_per_step": 25 * n},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,

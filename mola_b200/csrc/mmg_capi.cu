@@ -367,7 +367,7 @@ static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy,
         static const unsigned bs = [] {  // block size, tunable for the profiles (MMG_NN_BLOCK = 64 | 128 | 256)
             const char* e = getenv("MMG_NN_BLOCK");
             const int   v = e ? atoi(e) : 0;
-            return (unsigned)((v == 64 || v == 128 || v == 256) ? v : 256);
+            return (unsigned)((v == 64 || v == 128 || v == 256) ? v : 128);
         }();
         const unsigned nb = (unsigned)std::min<size_t>((nq + bs - 1) / bs, (size_t)m->num_sms * 64 * (256 / bs));
         MMG_LAUNCH((k_nn_single_pruned<Tr>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);

@@ -223,6 +223,19 @@ void GpuPointMapBase::nn_radius_search_batch(const float* xs, const float* ys, c
     if (total) check(mmg_nn_radius_fetch(h_, reinterpret_cast<float*>(out.points.data()), out.dist_sqr.data(), out.ids.data(), MMG_MEM_HOST, nullptr));
 }
 
+void GpuPointMapBase::match_points_batch(const float* xs, const float* ys, const float* zs, size_t n, float max_dist_sqr, NNBatchResult& out,
+                                         const std::optional<const mrpt::poses::CPose3D>& pose) const
+{
+    syncParams();
+    const PoseArg P(pose);
+    out.local_idx.resize(n), out.points.resize(n), out.dist_sqr.resize(n), out.ids.resize(n);
+    uint64_t m = 0;
+    check(mmg_match_batch(h_, xs, ys, zs, n, P.ptr, max_dist_sqr, &m, out.local_idx.data(), reinterpret_cast<float*>(out.points.data()),
+                          out.dist_sqr.data(), out.ids.data(), MMG_MEM_HOST, nullptr));
+    out.local_idx.resize(m), out.points.resize(m), out.dist_sqr.resize(m), out.ids.resize(m);
+}
+void GpuPointMapBase::reserve(uint64_t voxels) { check(mmg_reserve(h_, voxels)); }
+
 bool GpuPointMapBase::nn_single_search(const mrpt::math::TPoint3Df& q, mrpt::math::TPoint3Df& result, float& d2, uint64_t& id) const
 {  // HashedVoxelPointCloud.cpp:666-679
     NNBatchResult r;

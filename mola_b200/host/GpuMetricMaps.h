@@ -45,6 +45,7 @@ struct NNBatchResult
     std::vector<mrpt::math::TPoint3Df> points;
     std::vector<float>                 dist_sqr;
     std::vector<uint64_t>              ids;
+    std::vector<uint32_t>              local_idx;  // match_points_batch: index of the local point of each pairing
 };
 
 /** Code shared by the three map classes: owns the mmg_map handle (deep-copied on copy). */
@@ -96,6 +97,13 @@ class GpuPointMapBase : public mrpt::maps::CMetricMap, public mrpt::maps::Neares
                                   const std::optional<const mrpt::poses::CPose3D>& pose = std::nullopt) const;
     void nn_radius_search_batch(const float* xs, const float* ys, const float* zs, size_t n, float search_radius_sqr, size_t maxPoints,
                                 NNBatchResult& out, const std::optional<const mrpt::poses::CPose3D>& pose = std::nullopt) const;
+
+    /** Batched distance-threshold matcher (what mp2p_icp's Matcher_Points_DistanceThreshold does with one nn_single_search
+     *  per point): pairings (local_idx, map point, d2, id) with d2 < max_dist_sqr, in local-point order; one C-ABI call. */
+    void match_points_batch(const float* xs, const float* ys, const float* zs, size_t n, float max_dist_sqr, NNBatchResult& out,
+                            const std::optional<const mrpt::poses::CPose3D>& pose = std::nullopt) const;
+    /** voxels_.reserve() of the reference's insert (HashedVoxelPointCloud.cpp:1070) */
+    void reserve(uint64_t voxels);
 
     // --- contents
     void   visitAllPoints(const std::function<void(const mrpt::math::TPoint3Df&)>& f) const;

@@ -255,6 +255,19 @@ static void run_case(Oracle& O, const Case& c)
         mg::NNBatchResult b;
         m->nn_single_search_batch(qx.data(), qy.data(), qz.data(), nq, b);
         for (size_t i = 0; i < nq; i++) CHECK(b.found[i] == of[i] && (!of[i] || (b.ids[i] == oi[i] && same_bits(&b.dist_sqr[i], &od[i], 1))));
+        {   // batched matcher == per-point results filtered by 'd2 < thr^2', in order
+            const float   t2 = 0.04f;
+            mg::NNBatchResult pm;
+            m->match_points_batch(qx.data(), qy.data(), qz.data(), nq, t2, pm);
+            size_t k = 0;
+            for (size_t i = 0; i < nq; i++)
+                if (of[i] && od[i] < t2)
+                {
+                    CHECK(k < pm.local_idx.size() && pm.local_idx[k] == i && pm.ids[k] == oi[i] && same_bits(&pm.dist_sqr[k], &od[i], 1));
+                    k++;
+                }
+            CHECK(k == pm.local_idx.size() && k > 0);
+        }
         for (size_t K : {size_t(1), size_t(2), size_t(3)})
         {
             std::vector<uint32_t> oc(nq);
