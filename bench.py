@@ -428,6 +428,8 @@ def main():
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keeps NCCL's version banner out of stdout: the JSON line stays alone there
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
         run_gpu(args, rank, world, local_rank)

@@ -15,8 +15,9 @@
 // schedule). The free slots' float4.w lanes serve as the scratch (0 = empty; stored points keep
 // w == 0), so the ranking needs no memory of its own. Three exact prunings keep it cheap:
 // full voxels drop their points right after the probe; a point with w earlier same-voxel peers
-// in its warp starts at slot w (>= its final rank); and a point later than the voxel's last
-// free slot's current holder is dropped (slots only ever move to earlier indices).
+// in its warp starts at slot w (>= its final rank); a point later than the voxel's last free
+// slot's current holder is dropped (slots only ever move to earlier indices); and the prefix of
+// slots that already hold earlier points is skipped with plain loads before the first atomic.
 //
 // k_insert_commit (one warp per touched voxel): turns the ranked indices into stored points
 // (compose is recomputed, it is deterministic), running mean for SparseVoxel, bounding box,
@@ -48,16 +49,41 @@ __device__ __forceinline__ const PoseD& scan_pose(const ScanSet& S, u32 gi)
     return S.poses[lo];
 }
 
+// scan of point gi, given the scan of an earlier point of the same block (scans are long, so this is 0 or 1 step)
+__device__ __forceinline__ u32 scan_from(const ScanSet& S, u32 s0, u32 gi)
+{
+    while (s0 + 1 < S.nscans && __ldg(S.offsets + s0 + 1) <= gi) s0++;
+    return s0;
+}
+__device__ __forceinline__ u32 scan_index(const ScanSet& S, u32 gi)
+{
+    u32 lo = 0, hi = S.nscans;
+    while (hi - lo > 1)
+    {
+        const u32 mid = (lo + hi) >> 1;
+        if (__ldg(S.offsets + mid) <= gi) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
 __device__ __forceinline__ u32* slot_w(float4* p) { return reinterpret_cast<u32*>(p) + 3; }
 
-// find-or-insert that also returns the voxel's published point count
+// find-or-insert that also returns the voxel's published point count. One 16-byte L2 load (ld.cg) per probe returns
+// key, row id and count together. A voxel created by THIS batch has count 0 until k_insert_commit runs, so a reader that
+// has to wait for the creator's row id (or still sees the 0xFFFFFFFF of the never-used entry) knows the count is 0.
 __device__ __forceinline__ u32 find_or_insert_cnt(const VoxelMapDev& m, u64 key, u32& cnt)
 {
     u64 h = hash_key(key) & m.mask;
     for (;;)
     {
-        Entry* e = m.table + h;
-        u64    k = *reinterpret_cast<volatile u64*>(&e->key);
+        Entry*      e = m.table + h;
+        const uint4 v = __ldcg(reinterpret_cast<const uint4*>(e));
+        u64         k = (u64)v.x | ((u64)v.y << 32);
+        if (k == key && v.z != VID_INVALID)
+        {
+            cnt = v.w == 0xFFFFFFFFu ? 0u : v.w;
+            return v.z;
+        }
         if (k == KEY_EMPTY)
         {
             k = atomicCAS(reinterpret_cast<u64*>(&e->key), KEY_EMPTY, key);
@@ -72,12 +98,11 @@ __device__ __forceinline__ u32 find_or_insert_cnt(const VoxelMapDev& m, u64 key,
             }
         }
         if (k == key)
-        {
-            u32 v;
-            while ((v = *reinterpret_cast<volatile u32*>(&e->vid)) == VID_INVALID) {}
-            __threadfence();
-            cnt = *reinterpret_cast<volatile u32*>(&e->cnt);
-            return v;
+        {   // being created by another thread of this batch
+            u32 r;
+            while ((r = *reinterpret_cast<volatile u32*>(&e->vid)) == VID_INVALID) {}
+            cnt = 0;
+            return r;
         }
         h = (h + 1) & m.mask;
     }
@@ -118,14 +143,21 @@ __global__ void __launch_bounds__(256)
 {
     constexpr int  CAP = Tr::CAP;
     __shared__ u32 sm_bbox[8][6];
+    __shared__ u32 sm_scan;
     const u32      i     = blockIdx.x * blockDim.x + threadIdx.x;
     const bool     valid = i < n;
     float3         g     = make_float3(0.f, 0.f, 0.f);
     int            cx = 0, cy = 0, cz = 0;
     bool           ok = false;
+    if (S.poses)
+    {   // one binary search per block instead of one per point
+        if (threadIdx.x == 0) sm_scan = scan_index(S, base + blockIdx.x * blockDim.x);
+        __syncthreads();
+    }
     if (valid)
     {
-        g  = compose_point(scan_pose(S, base + i), xs[i], ys[i], zs[i]);
+        const float lx = xs[i], ly = ys[i], lz = zs[i];
+        g = compose_point(S.poses ? S.poses[scan_from(S, sm_scan, base + i)] : S.single, lx, ly, lz);
         ok = Tr::to_index(g.x, inv, cx) & Tr::to_index(g.y, inv, cy) & Tr::to_index(g.z, inv, cz);
         if (!ok) atomicAdd(&m.ctr->oob, 1u);
     }
@@ -145,8 +177,30 @@ __global__ void __launch_bounds__(256)
         u32       s     = __popc(peers & ((1u << lane) - 1u));  // earlier same-voxel points of this warp
         float4*   row   = m.pts + (size_t)vid * CAP + n0;
         u32       x     = ~i;                                   // larger = earlier; never 0 (i < 2^31)
-        if (s < room && !(*reinterpret_cast<volatile u32*>(slot_w(row + room - 1)) > x))
+        if (s < room)
         {
+            // Plain loads first (issued together): the last free slot (a point later than its holder can never get in: slots
+            // only move to earlier indices) and the prefix of slots already held by earlier points (a slot value only ever
+            // grows, so this point can never settle there, and that many earlier points of the voxel exist: its final rank is
+            // at least that). Points arriving in input order then need ONE atomic instead of walking the filled prefix.
+            u32 wl = *reinterpret_cast<volatile u32*>(slot_w(row + room - 1));
+            for (;;)
+            {
+                u32 w[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) w[k] = (s + k < room) ? *reinterpret_cast<volatile u32*>(slot_w(row + s + k)) : 0u;
+                if (wl > x)
+                {
+                    s = room;
+                    break;
+                }
+                int adv = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (adv == k && w[k] > x) adv = k + 1;
+                s += adv;
+                if (adv < 4 || s >= room) break;
+            }
             for (; s < room; s++)
             {
                 const u32 old = atomicMax(slot_w(row + s), x);
