@@ -234,11 +234,13 @@ def run_c4(ctx):
             if ctx.world > 1:
                 dist.all_reduce(hits)
             sweep.append({"r": r, "maxPoints": mp, "ms": ms, "qps": nq_total / ms * 1e3, "hits": int(hits[0])})
+    nn_ms = max_over_ranks(ev_time(ctx.stream, lambda: g.nn_single_search_batch(dq[0], dq[1], dq[2]), reps=3), ctx.world, ctx.dev)
     if ctx.rank != 0:
         return None
     out = {"config": "c4", "workload": f"SparseTreesPointCloud grid 10 m, clearance 0.05: nn_radius_search sweep, {nq_total} queries sharded x{ctx.world}",
            "n_gpus": ctx.world, "stored_points": int(g.numPoints()), "blocks": int(g.numVoxels()), "scans": nscans, "points_in": n_in,
-           "insert_s": build_s, "insert_mpts_s": n_in / build_s / 1e6 if build_s else None, "bcast_s": bcast_s, "sweep": sweep}
+           "insert_s": build_s, "insert_mpts_s": n_in / build_s / 1e6 if build_s else None, "bcast_s": bcast_s, "nn_single_ms": nn_ms,
+           "nn_single_qps": nq_total / nn_ms * 1e3, "sweep": sweep}
     # CPU parity + baseline on a reduced twin (the reference's per-block kd-tree rebuild makes a 50M-pt CPU build impractical here)
     if a.c4_cpu_scans > 0:
         kind = bench.cpu_lib_kind()

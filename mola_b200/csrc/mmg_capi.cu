@@ -370,7 +370,22 @@ static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy,
             return (unsigned)((v == 64 || v == 128 || v == 256) ? v : 128);
         }();
         const unsigned nb = (unsigned)std::min<size_t>((nq + bs - 1) / bs, (size_t)m->num_sms * 64 * (256 / bs));
-        MMG_LAUNCH((k_nn_single_pruned<Tr>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);
+        // tuning knobs for the profiles: MMG_NN_VARIANT = <min blocks of 256 per SM: 5 (default) | 6 | 8><p for packed f32x2 math>
+        static const int tv = [] {
+            const char* e = getenv("MMG_NN_VARIANT");
+            if (!e) return 1;  // measured best on C2: 48 registers (5 blocks of 256 per SM), packed x/y math
+            const int mb = atoi(e), pk = strchr(e, 'p') != nullptr;
+            return (mb == 8 ? 2 : mb == 6 ? 1 : 0) * 2 + pk;
+        }();
+        switch (tv)
+        {
+            case 1: MMG_LAUNCH((k_nn_single_pruned<Tr, 5, true>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
+            case 2: MMG_LAUNCH((k_nn_single_pruned<Tr, 6, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
+            case 3: MMG_LAUNCH((k_nn_single_pruned<Tr, 6, true>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
+            case 4: MMG_LAUNCH((k_nn_single_pruned<Tr, 8, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
+            case 5: MMG_LAUNCH((k_nn_single_pruned<Tr, 8, true>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
+            default: MMG_LAUNCH((k_nn_single_pruned<Tr, 5, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
+        }
     }
 }
 

@@ -44,6 +44,7 @@ enum ScratchSlot
     S_TREES1,
     S_TREES2,
     S_TREES3,
+    S_TREES_TODO,
     S_COUNT
 };
 struct TreesState;

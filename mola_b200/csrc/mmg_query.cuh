@@ -208,8 +208,22 @@ __device__ __forceinline__ void nn_axis_gaps(int c, float vsize, float q, float 
     }
 }
 
+// (dx*dx + dy*dy) + dz*dz with the x/y lanes as one packed FADD2 + FMUL2 (sm_100 f32x2, IEEE round-to-nearest per lane:
+// bit-identical to sqr_dist); t.x/t.y arrive as an aligned register pair from the LDG.128, so no moves are needed.
+__device__ __forceinline__ float sqr_dist_packed(const float4& t, unsigned long long qxy, float qz)
+{
+    unsigned long long a, d, mm;
+    float              mx, my;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(a) : "f"(t.x), "f"(t.y));
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(qxy));
+    asm("mul.rn.f32x2 %0, %1, %1;" : "=l"(mm) : "l"(d));
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(mx), "=f"(my) : "l"(mm));
+    const float dz = __fsub_rn(t.z, qz);
+    return __fadd_rn(__fadd_rn(mx, my), __fmul_rn(dz, dz));
+}
+
 // visits one stencil cell b (0..26) for this thread's query; merges into (bd, br, bv)
-template <class Tr>
+template <class Tr, bool PACKED = false>
 __device__ __forceinline__ void nn_visit_cell(const VoxelMapDev& m, int b, int cx, int cy, int cz, const float3& p, float& bd, u32& br, u32& bv)
 {
     constexpr int CAP = Tr::CAP;
@@ -221,19 +235,21 @@ __device__ __forceinline__ void nn_visit_cell(const VoxelMapDev& m, int b, int c
     // inside a cell the slots come in ascending order, so a strict '<' keeps the first minimum
     float cd = __int_as_float(0x7f800000);
     u32   cs = 0;
+    unsigned long long qxy = 0;
+    if (PACKED) asm("mov.b64 %0, {%1,%2};" : "=l"(qxy) : "f"(p.x), "f"(p.y));
 #pragma unroll 4
     for (u32 s = 0; s < cnt; s++)
     {
         const float4 t = __ldg(row + s);
-        const float  d = sqr_dist(t.x, t.y, t.z, p.x, p.y, p.z);
+        const float  d = PACKED ? sqr_dist_packed(t, qxy, p.z) : sqr_dist(t.x, t.y, t.z, p.x, p.y, p.z);
         if (d < cd) cd = d, cs = s;
     }
     const u32 rank = (u32)b * 32u + cs;
     if (cnt && (cd < bd || (cd == bd && rank < br))) bd = cd, br = rank, bv = vid;
 }
 
-template <class Tr>
-__global__ void __launch_bounds__(256)
+template <class Tr, int MINB = 1, bool PACKED = false>
+__global__ void __launch_bounds__(256, MINB)
     k_nn_single_pruned(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride,
                        PoseD pose, int use_pose, float inv, float vsize, QueryOut out, float bd_init)
 {
@@ -265,7 +281,7 @@ __global__ void __launch_bounds__(256)
             nn_axis_gaps<Tr>(cy, vsize, p.y, gy);
             nn_axis_gaps<Tr>(cz, vsize, p.z, gz);
             // the query's own voxel first: it nearly always holds the answer and sets the bound
-            nn_visit_cell<Tr>(m, 13, cx, cy, cz, p, bd, br, bv);
+            nn_visit_cell<Tr, PACKED>(m, 13, cx, cy, cz, p, bd, br, bv);
             // this thread's own work list: the neighbours whose box can still matter
             u32 todo = 0;
 #pragma unroll
@@ -279,7 +295,7 @@ __global__ void __launch_bounds__(256)
                 const float lb = (ix == 0 ? gx[0] : ix == 1 ? gx[1] : gx[2]) + (iy == 0 ? gy[0] : iy == 1 ? gy[1] : gy[2]) +
                                  (iz == 0 ? gz[0] : iz == 1 ? gz[1] : gz[2]);
                 if (lb > bd) continue;  // the bound has tightened since the list was made
-                nn_visit_cell<Tr>(m, b, cx, cy, cz, p, bd, br, bv);
+                nn_visit_cell<Tr, PACKED>(m, b, cx, cy, cz, p, bd, br, bv);
             }
         }
         const bool found = br != 0xFFFFFFFFu;

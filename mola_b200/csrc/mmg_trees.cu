@@ -234,6 +234,29 @@ int trees_clone(const mmg_map* src, mmg_map* dst)
 }
 
 // ------------------------------------------------------------------ insert
+// nn_single_search on the device: the thread-per-query fast path, then the warp-per-query branch and bound for the
+// queries it could not certify (no host round trip: the second kernel reads the list length on the device).
+static int launch_trees_nn1(mmg_map* m, const float* qx, const float* qy, const float* qz, size_t nq, u32 stride, const PoseD& T, int use_pose,
+                            float notfound_d2, uint8_t* df, float* dxyz, float* dd2, u64* did, cudaStream_t st)
+{
+    static const bool slow_only = getenv("MMG_TREES_NN_SLOW") != nullptr;  // A/B switch for the profiles
+    const unsigned    nb        = persistent_blocks(m, nq, 8, 8);
+    if (slow_only)
+    {
+        MMG_LAUNCH(k_trees_nn1, nb, 256, 0, st, m->trees->dev, qx, qy, qz, (u32)nq, stride, T, use_pose, notfound_d2, df, dxyz, dd2, did, (const u32*)nullptr,
+                   (const u32*)nullptr);
+        return MMG_OK;
+    }
+    u32* todo = (u32*)m->scratch_get(S_TREES_TODO, (nq + 1) * sizeof(u32));
+    if (!todo) return MMG_ERR_OUT_OF_MEM;
+    MMG_CUDA(cudaMemsetAsync(todo + nq, 0, sizeof(u32), st));
+    MMG_LAUNCH(k_trees_nn1_fast, (unsigned)((nq + 255) / 256), 256, 0, st, m->trees->dev, qx, qy, qz, (u32)nq, stride, T, use_pose, notfound_d2, df, dxyz, dd2,
+               did, todo, todo + nq);
+    MMG_LAUNCH(k_trees_nn1, nb, 256, 0, st, m->trees->dev, qx, qy, qz, (u32)nq, stride, T, use_pose, notfound_d2, df, dxyz, dd2, did, (const u32*)todo,
+               (const u32*)(todo + nq));
+    return MMG_OK;
+}
+
 int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, int has_robot_pose, int mem,
                  cudaStream_t st)
 {
@@ -283,8 +306,7 @@ int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     const PoseD T = make_pose(pose12);
     MMG_LAUNCH(k_trees_compose, gN, 256, 0, st, dx, dy, dz, N, T, gp);
     const float*   gq = (const float*)gp;
-    const unsigned nb = persistent_blocks(m, n, 8, 8);
-    MMG_LAUNCH(k_trees_nn1, nb, 256, 0, st, s->dev, gq, gq + 1, gq + 2, N, 4u, T, 0, -1.0f, (uint8_t*)nullptr, (float*)nullptr, d2, (u64*)nullptr);
+    if ((rc = launch_trees_nn1(m, gq, gq + 1, gq + 2, n, 4u, T, 0, -1.0f, (uint8_t*)nullptr, (float*)nullptr, d2, (u64*)nullptr, st))) return rc;
     const float thr = P.minimum_points_clearance * P.minimum_points_clearance;
     MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->oob, 0, sizeof(u32), st));
     MMG_LAUNCH(k_trees_flags, gN, 256, 0, st, s->dev, gp, d2, N, thr, flag);
@@ -349,8 +371,7 @@ int trees_nn_single(const mmg_map* cm, const float* xs, const float* ys, const f
         did = (u64*)ob, dxyz = (float*)(ob + nq * 8), dd2 = (float*)(ob + nq * 20), df = (uint8_t*)(ob + nq * 24);
     }
     const PoseD    T  = make_pose(pose12);
-    const unsigned nb = persistent_blocks(m, nq, 8, 8);
-    MMG_LAUNCH(k_trees_nn1, nb, 256, 0, st, m->trees->dev, dx, dy, dz, (u32)nq, (u32)stride, T, pose12 ? 1 : 0, 0.0f, df, dxyz, dd2, did);
+    if ((rc = launch_trees_nn1(m, dx, dy, dz, nq, (u32)stride, T, pose12 ? 1 : 0, 0.0f, df, dxyz, dd2, did, st))) return rc;
     MMG_CUDA(cudaGetLastError());
     if (mem == MMG_MEM_HOST)
     {

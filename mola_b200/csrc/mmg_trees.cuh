@@ -350,12 +350,15 @@ __device__ __forceinline__ bool trees_find_block(const TreesDev& t, float x, flo
 // ties to the lowest block-local index. One warp per query.
 static __global__ void __launch_bounds__(256)
     k_trees_nn1(TreesDev t, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride, PoseD pose,
-                int use_pose, float notfound_d2, uint8_t* __restrict__ ofound, float* __restrict__ oxyz, float* __restrict__ od2, u64* __restrict__ oid)
+                int use_pose, float notfound_d2, uint8_t* __restrict__ ofound, float* __restrict__ oxyz, float* __restrict__ od2, u64* __restrict__ oid,
+                const u32* __restrict__ list /*nullable: the queries k_trees_nn1_fast left open*/, const u32* __restrict__ nlist)
 {
     const int lane   = lane_id();
     const u32 nwarps = (gridDim.x * blockDim.x) >> 5;
-    for (u32 q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < n; q += nwarps)
+    if (list) n = *nlist;
+    for (u32 w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < n; w += nwarps)
     {
+        const u32    q  = list ? list[w] : w;
         const size_t qi = (size_t)q * stride;
         float3       p  = make_float3(qx[qi], qy[qi], qz[qi]);
         if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
@@ -387,6 +390,85 @@ static __global__ void __launch_bounds__(256)
             if (oid) oid[q] = 0;
         }
     }
+}
+
+// nn_single_search fast path: one THREAD per query looks only at the 27 fine cells around the query. The answer is final
+// when it is provably the block-wide one: its d2 lies strictly below the squared distance from the query to the nearest
+// face of that 3x3x3 cell region that is interior to the block (everything filed outside the region is farther, so neither
+// a closer point nor an equal-distance tie with a lower index can exist there). ICP-style queries (a scan re-posed by a
+// few centimetres against a 0.31 m cell grid) nearly always certify; the rest are listed in `todo` and answered by the
+// warp-per-query branch and bound (k_trees_nn1 with that list). Same results either way.
+static __global__ void __launch_bounds__(256)
+    k_trees_nn1_fast(TreesDev t, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride, PoseD pose,
+                     int use_pose, float notfound_d2, uint8_t* __restrict__ ofound, float* __restrict__ oxyz, float* __restrict__ od2, u64* __restrict__ oid,
+                     u32* __restrict__ todo, u32* __restrict__ ntodo)
+{
+    const u32 q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const size_t qi = (size_t)q * stride;
+    float3       p  = make_float3(qx[qi], qy[qi], qz[qi]);
+    if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
+    int   kx, ky, kz;
+    u32   bid = 0;
+    float bd  = __int_as_float(0x7f800000);
+    u32   bi  = 0xFFFFFFFFu;
+    float bx = 0.f, by = 0.f, bz = 0.f;
+    bool  final_ = true;  // no block: nothing to find (SparseTreesPointCloud.cpp:617-619)
+    if (trees_find_block(t, p.x, p.y, p.z, kx, ky, kz, bid))
+    {
+        const BlockGeom g    = trees_geom(t, kx, ky, kz);
+        const float     qv[3] = {p.x, p.y, p.z};
+        int             c0[3];
+#pragma unroll
+        for (int a = 0; a < 3; a++) c0[a] = trees_cell_axis(g, a, qv[a]);
+        // own cell first (sets the bound), then the 26 neighbours that can still matter
+        for (int it = 0; it < 27; it++)
+        {
+            const int j = it == 0 ? 13 : (it <= 13 ? it - 1 : it);
+            const int x = c0[0] + j / 9 - 1, y = c0[1] + (j / 3) % 3 - 1, z = c0[2] + j % 3 - 1;
+            if (x < 0 || x > 31 || y < 0 || y > 31 || z < 0 || z > 31) continue;
+            const u32 cell = trees_cell_id(x, y, z);
+            if (!((__ldg(&t.l0[(size_t)bid * 1024 + (cell >> 5)]) >> (cell & 31)) & 1u)) continue;
+            if (it && trees_box_lb(g, qv, x, y, z, 1) > bd) continue;
+            u32 head, cnt;
+            if (!probe_ro(t.ctab, t.cmask, trees_cell_key(bid, cell), head, cnt) || cnt == 0) continue;
+            u32 fill = ((cnt - 1) & (TR_ROW - 1)) + 1, row = head;
+            for (u32 r = 0, nrows = (cnt + TR_ROW - 1) / TR_ROW; r < nrows; r++)
+            {
+                const float4* rp = t.cpts + (size_t)row * TR_ROW;
+                for (u32 s = 0; s < fill; s++)
+                {
+                    const float4 c = __ldg(rp + s);
+                    const float  d = sqr_dist(qv[0], qv[1], qv[2], c.x, c.y, c.z);
+                    const u32    i = __float_as_uint(c.w);
+                    if (d < bd || (d == bd && i < bi)) bd = d, bi = i, bx = c.x, by = c.y, bz = c.z;
+                }
+                row  = __ldg(&t.cnext[row]);
+                fill = TR_ROW;
+            }
+        }
+        // squared distance to the complement of the region inside the block (conservative, like trees_box_lb)
+        float out = __int_as_float(0x7f800000);
+#pragma unroll
+        for (int a = 0; a < 3; a++)
+        {
+            const int   lo_c = max(c0[a] - 1, 0), hi_c = min(c0[a] + 1, 31);
+            const float mg   = 8.f * g.margin[a];
+            if (lo_c > 0) out = fminf(out, fmaxf(0.f, qv[a] - (g.lo[a] + (float)lo_c * g.cs[a]) - mg));
+            if (hi_c < 31) out = fminf(out, fmaxf(0.f, (g.lo[a] + (float)(hi_c + 1) * g.cs[a]) - qv[a] - mg));
+        }
+        final_ = bi != 0xFFFFFFFFu && bd < out * out * 0.9999f;
+    }
+    if (!final_)
+    {
+        todo[atomicAdd(ntodo, 1u)] = q;
+        return;
+    }
+    const bool found = bi != 0xFFFFFFFFu;
+    if (ofound) ofound[q] = found ? 1 : 0;
+    if (oxyz) oxyz[3 * (size_t)q] = bx, oxyz[3 * (size_t)q + 1] = by, oxyz[3 * (size_t)q + 2] = bz;
+    od2[q] = found ? bd : notfound_d2;
+    if (oid) oid[q] = found ? (u64)bi : 0;
 }
 
 // nn_multiple_search (:626-643): k <= 32 nearest inside the block, ascending (d2, index)
