@@ -287,10 +287,14 @@ __global__ void __launch_bounds__(256, MINB)
 #pragma unroll
             for (int b = 0; b < 27; b++)
                 if (b != 13 && !(gx[b / 9] + gy[(b / 3) % 3] + gz[b % 3] > bd)) todo |= 1u << b;
+            // face neighbours first, then edges, then corners: the closer boxes tighten the bound soonest, so fewer of the
+            // later ones survive the re-check below (any order gives the same answer: the merge is on (d2, scan rank))
+            constexpr u32 FACE = 0x415410u, EDGE = 0x2aa8aaau;
             while (todo)
             {
-                const int b = __ffs(todo) - 1;
-                todo &= todo - 1;
+                const u32 tier = (todo & FACE) ? (todo & FACE) : ((todo & EDGE) ? (todo & EDGE) : todo);
+                const int b    = __ffs(tier) - 1;
+                todo &= ~(1u << b);
                 const int   ix = b / 9, iy = (b / 3) % 3, iz = b % 3;
                 const float lb = (ix == 0 ? gx[0] : ix == 1 ? gx[1] : gx[2]) + (iy == 0 ? gy[0] : iy == 1 ? gy[1] : gy[2]) +
                                  (iz == 0 ? gz[0] : iz == 1 ? gz[1] : gz[2]);
