@@ -70,3 +70,37 @@ def test_c2_stored_points_find_themselves(c2):
     cx = ((i >> np.uint64(5)) & np.uint64(0xFFFFF)).astype(np.int64)
     cx = np.where(cx >= 1 << 19, cx - (1 << 20), cx)
     assert np.array_equal(cx, gk[sel, 0].astype(np.int64))
+
+
+def test_c5_fused_insert_of_64_scans_matches_sequential_oracle(built):
+    """BASELINE config 5 at full size: 64 OS1-128 scans (16.8M points) inserted by ONE mmg_insert_scans call ==
+    the oracle inserting them one after the other (voxel set, counts, ordered point lists, bounding box), and a
+    second identical batch changes nothing but the already-full rows' neighbours (still equal to the oracle)."""
+    import torch
+    from mola_b200 import HashedVoxelPointCloud, synth
+    from oracle import mmo
+    ns = 64
+    scans = [synth.lidar_scan("os1_128", s=2.0 * k, seed=5, scan_id=k) for k in range(ns)]
+    off = np.concatenate([[0], np.cumsum([s[0].size for s in scans])]).astype(np.uint64)
+    poses = np.stack([s[3] for s in scans])
+    d = [torch.from_numpy(np.concatenate([s[a] for s in scans])).cuda() for a in range(3)]
+    g = HashedVoxelPointCloud(0.5)
+    o = mmo.OracleMap(0, 0.5)
+    for rep in range(2):
+        g.insertPointClouds(d[0], d[1], d[2], off, poses)
+        for s in scans:
+            o.insert(*s)
+        assert g.numPoints() == o.num_points() and g.numVoxels() == o.num_voxels()
+        gk, gc, gp, _ = g.exportVoxels()
+        ok, oc, op = o.export()
+        assert np.array_equal(gk, ok) and np.array_equal(gc, oc)
+        assert np.array_equal(gp.view(np.uint32), op.view(np.uint32))
+    assert np.array_equal(np.concatenate(g.boundingBox()), np.concatenate(o.bbox()))
+    # every scan queried against the finished map, one scan checked against the oracle
+    s = scans[31]
+    qpose = synth.perturbed_pose(s[3])
+    f, p, dd, ii = g.nn_single_search_batch(s[0], s[1], s[2], pose=qpose)
+    from conftest import compose_host
+    of, op_, od, oi = o.nn_single(*compose_host(qpose, s[0], s[1], s[2]), nthreads=8)
+    k = of > 0
+    assert np.array_equal(f, of) and np.array_equal(ii[k], oi[k]) and np.array_equal(dd[k].view(np.uint32), od[k].view(np.uint32))
