@@ -233,6 +233,11 @@ __device__ __forceinline__ void nn_visit_cell(const VoxelMapDev& m, int b, int c
     if (!probe_ro(m.table, m.mask, pack_key(x, y, z), vid, cnt)) return;
     const float4* row = m.pts + (size_t)vid * CAP;
     // inside a cell the slots come in ascending order, so a strict '<' keeps the first minimum
+    // a row spans up to four 128-byte lines: ask for the later ones now, so the walk below does not pay one L2 round
+    // trip per line
+    if (cnt > 8) asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 8));
+    if (cnt > 16) asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 16));
+    if (cnt > 24) asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 24));
     float cd = __int_as_float(0x7f800000);
     u32   cs = 0;
     unsigned long long qxy = 0;
