@@ -1,5 +1,7 @@
 #!/usr/bin/env python
-"""bench_configs.py — the other BASELINE.json configurations (bench.py is config 2, the headline).
+"""tests/bench_configs.py — the other BASELINE.json configurations (bench.py is config 2, the headline).
+Lives under tests/ because every leg checks the CUDA path against the CPU oracle (test infrastructure) while timing it.
+Run: python tests/bench_configs.py [--configs c1,c3,c4,c5]   (or under torchrun for the sharded legs)
 
   c1  one 120k-pt HDL-64 scan: HashedVoxelPointCloud (0.5 m) insert + nn_single_search, GPU vs the CPU reference, full parity
   c3  SparseVoxelPointCloud (0.2 m): nn_multiple_search k=8 (extension N4) + per-voxel mean/covariance
@@ -18,7 +20,7 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402  (compose_host, cpu_threads, cpu_lib_kind)
 
