@@ -402,9 +402,10 @@ def run_gpu(args, rank, world, local_rank):
     if batch_insert:
         batch_insert["frac_of_hbm_peak"] = batch_insert["achieved_gbs"] / peak
     achieved = bytes_per_q * n / (dev_ms / args.steps * 1e-3) / 1e9
-    traffic = None
+    traffic, ncu_note = None, None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("k_nn_single_dram_bytes_per_launch")
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic, ncu_note = tj.get("k_nn_single_dram_bytes_per_launch"), tj.get("k_nn_single_ncu")
     except Exception:
         pass
     line = {"metric": "nn_single_search queries/s", "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
@@ -418,7 +419,9 @@ def run_gpu(args, rank, world, local_rank):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "kernel": "k_nn_single_pruned<HashedTraits>", "algorithmic_bytes_per_query": bytes_per_q, "mean_stencil_points": pbar.value,
-                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650"},
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                         "dram_gbs_actual": (traffic * 1e-9 / (dev_ms / args.steps * 1e-3)) if traffic else None,
+                         "note": "frac > 1: the algorithmic bytes of SURVEY 8(d) never reach DRAM (exact pruning + L2 reuse); see ncu", "ncu": ncu_note},
             "clocks": clocks, "found_frac": found_frac, "wall_ms_per_step_incl_flush": 1e3 * wall_s / args.steps,
             "insert": {"mpts_s": n_in / (ins_ms[0] * 1e-3) / 1e6 if ins_ms[0] else None, "points_in": n_in, "scans": nscans,
                        "note": "the map build itself: per-scan calls interleaved with scan synthesis (and the CPU twin at N=1), summed CUDA-event time; "
