@@ -155,6 +155,7 @@ int mmg::ensure_rows(mmg_map* m, u64 rows, cudaStream_t st)
     if ((rc = grow_array(&m->dev.cnt, m->rowcap, newcap, 0, st))) return rc;
     if ((rc = grow_array(&m->dev.vkey, m->rowcap, newcap, 0xFF, st))) return rc;
     if ((rc = grow_array(&m->dev.free_list, m->rowcap, newcap, 0, st))) return rc;
+    if ((rc = grow_array(&m->dev.fill, m->rowcap, newcap, 0, st))) return rc;
     if (m->kind == MMG_SPARSE_VOXEL && (rc = grow_array(&m->dev.mean, m->rowcap, newcap, 0, st))) return rc;
     m->rowcap = newcap;
     return MMG_OK;
@@ -232,7 +233,7 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
         // already large or was reserved (mmg_reserve) for more
         const u64    room_rows = m->rowcap > m->h_nvox_hi ? m->rowcap - m->h_nvox_hi : 0;
         const u64    room_tab  = m->cap / 2 > live ? m->cap / 2 - live : 0;
-        const size_t k = std::min<size_t>(n - a, std::max<u64>({(u64)1 << 20, 4 * live, std::min<u64>((n - a + 3) / 4, (u64)4 << 20), std::min(room_rows, room_tab)}));
+        const size_t k = std::min<size_t>({n - a, (size_t)RANK_MAX_CHUNK, (size_t)std::max<u64>({(u64)1 << 20, 4 * live, std::min<u64>((n - a + 3) / 4, (u64)4 << 20), std::min(room_rows, room_tab)})});
         int          rc;
         if ((rc = ensure_table(m, live + k, st))) return rc;
         if ((rc = ensure_rows(m, (u64)m->h_nvox_hi + k, st))) return rc;
@@ -240,8 +241,11 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
         if (!touched) return MMG_ERR_OUT_OF_MEM;
         MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->nseg, 0, sizeof(u32), st));
         ScanSet S = S0;
-        MMG_LAUNCH((k_insert_rank<Tr>), (unsigned)((k + 255) / 256), 256, 0, st, dx + a, dy + a, dz + a, (u32)k, (u32)a, S, m->inv, m->dev, eff, touched,
-                   uncapped ? 1 : 0);
+        const unsigned rb = (unsigned)((k + RANK_BLOCK - 1) / RANK_BLOCK);
+        if (S.poses)
+            MMG_LAUNCH((k_insert_rank<Tr, true>), rb, RANK_BLOCK, 0, st, dx + a, dy + a, dz + a, (u32)k, (u32)a, S, m->inv, m->dev, eff, touched, uncapped ? 1 : 0);
+        else
+            MMG_LAUNCH((k_insert_rank<Tr, false>), rb, RANK_BLOCK, 0, st, dx + a, dy + a, dz + a, (u32)k, (u32)a, S, m->inv, m->dev, eff, touched, uncapped ? 1 : 0);
         const unsigned fb = persistent_blocks(m, k, 8, 8);
         MMG_LAUNCH((k_insert_commit<Tr>), fb, 256, 0, st, m->dev, touched, dx + a, dy + a, dz + a, (u32)a, S, m->inv, uncapped ? 0 : 1,
                    m->kind == MMG_SPARSE_VOXEL ? 1 : 0);
@@ -280,7 +284,7 @@ static int insert_voxel(mmg_map* m, const float* xs, const float* ys, const floa
     static const bool force_sorted = getenv("MMG_INSERT_SORTED") != nullptr;  // A/B switch for the profiles
     if (!use_thr && !force_sorted)
     {
-        ScanSet S{nullptr, nullptr, 1, make_pose(pose12)};
+        ScanSet S{nullptr, nullptr, 1, 0.f, make_pose(pose12)};
         u32     oob = 0;
         if ((rc = insert_ranked<Tr>(m, dx, dy, dz, n, S, st, &oob))) return rc;
         m->points_dirty = true;
@@ -698,7 +702,7 @@ int mmg_destroy(mmg_map* m)
     cudaSetDevice(m->device);
     cudaDeviceSynchronize();
     if (m->kind == MMG_SPARSE_TREES) trees_destroy(m);
-    cudaFree(m->dev.table), cudaFree(m->dev.pts), cudaFree(m->dev.cnt), cudaFree(m->dev.vkey), cudaFree(m->dev.mean), cudaFree(m->dev.free_list),
+    cudaFree(m->dev.table), cudaFree(m->dev.pts), cudaFree(m->dev.cnt), cudaFree(m->dev.vkey), cudaFree(m->dev.mean), cudaFree(m->dev.free_list), cudaFree(m->dev.fill),
         cudaFree(m->dev.ctr);
     if (m->h_ctr) cudaFreeHost(m->h_ctr);
     if (m->s_in)
@@ -815,7 +819,7 @@ int mmg_insert_scans(mmg_map* m, const float* xs, const float* ys, const float* 
     MMG_CUDA(cudaMemcpyAsync(sb, poses12, n_scans * sizeof(PoseD), cudaMemcpyHostToDevice, st));
     MMG_CUDA(cudaMemcpyAsync(sb + n_scans * sizeof(PoseD), off.data(), (n_scans + 1) * sizeof(u32), cudaMemcpyHostToDevice, st));
     MMG_CUDA(cudaStreamSynchronize(st));  // `off` is pageable and about to go out of scope
-    ScanSet S{(const PoseD*)sb, (const u32*)(sb + n_scans * sizeof(PoseD)), (u32)n_scans, make_pose(nullptr)};
+    ScanSet S{(const PoseD*)sb, (const u32*)(sb + n_scans * sizeof(PoseD)), (u32)n_scans, (float)((double)n_scans / (double)n), make_pose(nullptr)};
     u32     oob = 0;
     if (m->kind == MMG_HASHED_VOXEL) rc = insert_ranked<HashedTraits>(m, dx, dy, dz, n, S, st, &oob);
     else rc = insert_ranked<SparseVoxelTraits>(m, dx, dy, dz, n, S, st, &oob);

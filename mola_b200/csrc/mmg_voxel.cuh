@@ -33,6 +33,7 @@ struct VoxelMapDev
     u64*    vkey;
     float4* mean;
     u32*    free_list;
+    u32*    fill;  // per row: free slots handed out by the running insert batch (zero outside k_insert_rank/_commit)
     Counters* ctr;
 };
 
