@@ -229,11 +229,14 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
     for (size_t a = 0; a < n;)
     {
         const u64    live = m->h_nvox_hi - m->h_free_n;
-        // chunk: at least 1M points; up to 4M for big batches (worst case 2 GB of row headroom); more when the map is
-        // already large or was reserved (mmg_reserve) for more
+        // chunk: at least 1M points, up to 8M for big batches (worst case "every point opens a voxel": 4.3 GB of row
+        // headroom, 2 % of a B200's HBM), more when the map is already large or was reserved (mmg_reserve) for more;
+        // a short tail is taken along instead of paying another launch pair + counter read-back for it
         const u64    room_rows = m->rowcap > m->h_nvox_hi ? m->rowcap - m->h_nvox_hi : 0;
         const u64    room_tab  = m->cap / 2 > live ? m->cap / 2 - live : 0;
-        const size_t k = std::min<size_t>({n - a, (size_t)RANK_MAX_CHUNK, (size_t)std::max<u64>({(u64)1 << 20, 4 * live, std::min<u64>((n - a + 3) / 4, (u64)4 << 20), std::min(room_rows, room_tab)})});
+        u64          want      = std::max<u64>({(u64)1 << 20, 4 * live, std::min<u64>(n - a, (u64)8 << 20), std::min(room_rows, room_tab)});
+        if (n - a > want && n - a - want < want / 4) want = n - a;
+        const size_t k = std::min<size_t>({n - a, (size_t)RANK_MAX_CHUNK, (size_t)want});
         int          rc;
         if ((rc = ensure_table(m, live + k, st))) return rc;
         if ((rc = ensure_rows(m, (u64)m->h_nvox_hi + k, st))) return rc;
@@ -705,6 +708,7 @@ int mmg_destroy(mmg_map* m)
     cudaFree(m->dev.table), cudaFree(m->dev.pts), cudaFree(m->dev.cnt), cudaFree(m->dev.vkey), cudaFree(m->dev.mean), cudaFree(m->dev.free_list), cudaFree(m->dev.fill),
         cudaFree(m->dev.ctr);
     if (m->h_ctr) cudaFreeHost(m->h_ctr);
+    if (m->h_stage) cudaFreeHost(m->h_stage);
     if (m->s_in)
     {
         cudaStreamDestroy(m->s_in), cudaStreamDestroy(m->s_out), cudaEventDestroy(m->ev_start);
@@ -814,11 +818,20 @@ int mmg_insert_scans(mmg_map* m, const float* xs, const float* ys, const float* 
     if (rc) return rc;
     char* sb = (char*)m->scratch_get(S_SCANS, n_scans * sizeof(PoseD) + (n_scans + 1) * sizeof(u32));
     if (!sb) return MMG_ERR_OUT_OF_MEM;
-    std::vector<u32> off(n_scans + 1);
+    // poses + 32-bit offsets go through a pinned staging block: one async copy, no sync (insert_ranked() below ends with
+    // a counter read-back on the same stream, so the block is free again when this call returns)
+    const size_t sbytes = n_scans * sizeof(PoseD) + (n_scans + 1) * sizeof(u32);
+    if (m->h_stage_bytes < sbytes)
+    {
+        if (m->h_stage) cudaFreeHost(m->h_stage);
+        m->h_stage = nullptr, m->h_stage_bytes = 0;
+        MMG_CUDA(cudaMallocHost(&m->h_stage, sbytes * 2));
+        m->h_stage_bytes = sbytes * 2;
+    }
+    memcpy(m->h_stage, poses12, n_scans * sizeof(PoseD));
+    u32* off = (u32*)((char*)m->h_stage + n_scans * sizeof(PoseD));
     for (size_t s = 0; s <= n_scans; s++) off[s] = (u32)scan_offsets[s];
-    MMG_CUDA(cudaMemcpyAsync(sb, poses12, n_scans * sizeof(PoseD), cudaMemcpyHostToDevice, st));
-    MMG_CUDA(cudaMemcpyAsync(sb + n_scans * sizeof(PoseD), off.data(), (n_scans + 1) * sizeof(u32), cudaMemcpyHostToDevice, st));
-    MMG_CUDA(cudaStreamSynchronize(st));  // `off` is pageable and about to go out of scope
+    MMG_CUDA(cudaMemcpyAsync(sb, m->h_stage, sbytes, cudaMemcpyHostToDevice, st));
     ScanSet S{(const PoseD*)sb, (const u32*)(sb + n_scans * sizeof(PoseD)), (u32)n_scans, (float)((double)n_scans / (double)n), make_pose(nullptr)};
     u32     oob = 0;
     if (m->kind == MMG_HASHED_VOXEL) rc = insert_ranked<HashedTraits>(m, dx, dy, dz, n, S, st, &oob);

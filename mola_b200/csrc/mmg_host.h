@@ -60,6 +60,8 @@ struct mmg_map
     mmg::u64         cap = 0, rowcap = 0;
     mmg::u32         h_nvox_hi = 0, h_free_n = 0;
     mmg::Counters*   h_ctr = nullptr;  // pinned mirror
+    void*            h_stage = nullptr;  // pinned staging block (scan poses + offsets of mmg_insert_scans)
+    size_t           h_stage_bytes = 0;
     bool             points_dirty = false;
     // radius results of the last mmg_nn_radius_batch
     mmg::u64  rad_total = 0;
