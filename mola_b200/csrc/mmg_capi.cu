@@ -99,6 +99,11 @@ static int init_counters(mmg_map* m, bool keep_bbox)
 int mmg::alloc_table(mmg_map* m, u64 cap)
 {
     Entry* t = nullptr;
+    if (cap > (1ull << 32))
+    {   // hash_key() yields 32 bits
+        set_error("voxel table of %llu entries exceeds the 2^32-entry limit", (unsigned long long)cap);
+        return MMG_ERR_OUT_OF_MEM;
+    }
     if (cudaMalloc(&t, cap * sizeof(Entry)) != cudaSuccess)
     {
         set_error("cudaMalloc table (%llu entries) failed", (unsigned long long)cap);

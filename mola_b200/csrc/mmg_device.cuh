@@ -121,14 +121,16 @@ __device__ __host__ __forceinline__ void unpack_key(u64 k, int& cx, int& cy, int
     cz = (int)((k >> 42) & 0x1FFFFF) - IDX_LIMIT;
 }
 __device__ __host__ __forceinline__ u64 hash_key(u64 k)
-{  // murmur3 finaliser: the reference's 20-bit Teschner hash (index3d_t.h:83-101) is not
-   // observable in results and clusters badly beyond 1M buckets, so the table uses its own.
-    k ^= k >> 33;
-    k *= 0xFF51AFD7ED558CCDull;
-    k ^= k >> 33;
-    k *= 0xC4CEB9FE1A85EC53ull;
-    k ^= k >> 33;
-    return k;
+{  // 32-bit multiply-xorshift mix of the two key halves (7 integer instructions; tables stay far below 2^32 entries).
+   // The reference's 20-bit Teschner hash (index3d_t.h:83-101) is not observable in results and clusters badly beyond
+   // 1M buckets, so the table uses its own.
+    u32 h = (u32)k * 0x85EBCA6Bu ^ (u32)(k >> 32) * 0xC2B2AE35u;
+    h ^= h >> 15;
+    h *= 0x2C1B3C6Du;
+    h ^= h >> 12;
+    h *= 0x297A2D39u;
+    h ^= h >> 15;
+    return h;
 }
 // g2plain: slot bits + 3 x 20 index bits (HashedVoxelPointCloud.h:95-108, SparseVoxelPointCloud.h:127-140).
 template <int SLOT_BITS>

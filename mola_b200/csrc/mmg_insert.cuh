@@ -310,7 +310,7 @@ __global__ void __launch_bounds__(256)
         if (take)
         {
             const u32    i = ~w;
-            const float3 g = compose_point(scan_pose(S, base + i), xs[i], ys[i], zs[i]);
+            const float3 g = compose_point(S.poses ? S.poses[scan_guess(S, base + i)] : S.single, __ldg(xs + i), __ldg(ys + i), __ldg(zs + i));
             p              = make_float4(g.x, g.y, g.z, 0.f);
             *slot          = p;  // also clears the ranking scratch in .w
         }
