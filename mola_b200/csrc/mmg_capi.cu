@@ -8,6 +8,7 @@
 #include "mmg_insert.cuh"
 
 #include <algorithm>
+#include <cstddef>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -228,9 +229,11 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
     const u32         hard     = (u32)Tr::CAP;
     const bool        uncapped = (P.max_points_per_voxel == 0 || P.max_points_per_voxel > hard);
     const u32         eff      = uncapped ? hard : P.max_points_per_voxel;
-    MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->oob, 0, sizeof(u32), st));
+    MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->oob, 0, 2 * sizeof(u32), st));  // oob, nseg: they run on from chunk to chunk
+    static_assert(offsetof(Counters, nseg) == offsetof(Counters, oob) + sizeof(u32), "oob and nseg are cleared by one memset");
     Counters c;
     memset(&c, 0, sizeof(c));
+    u32 seg_base = 0;
     for (size_t a = 0; a < n;)
     {
         const u64    live = m->h_nvox_hi - m->h_free_n;
@@ -247,18 +250,22 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
         if ((rc = ensure_rows(m, (u64)m->h_nvox_hi + k, st))) return rc;
         u32* touched = (u32*)m->scratch_get(S_SEG, k * sizeof(u32));
         if (!touched) return MMG_ERR_OUT_OF_MEM;
-        MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->nseg, 0, sizeof(u32), st));
         ScanSet S = S0;
         const unsigned rb = (unsigned)((k + RANK_BLOCK - 1) / RANK_BLOCK);
         if (S.poses)
-            MMG_LAUNCH((k_insert_rank<Tr, true>), rb, RANK_BLOCK, 0, st, dx + a, dy + a, dz + a, (u32)k, (u32)a, S, m->inv, m->dev, eff, touched, uncapped ? 1 : 0);
+            MMG_LAUNCH((k_insert_rank<Tr, true>), rb, RANK_BLOCK, 0, st, dx + a, dy + a, dz + a, (u32)k, (u32)a, S, m->inv, m->dev, eff, touched, seg_base,
+                       uncapped ? 1 : 0);
         else
-            MMG_LAUNCH((k_insert_rank<Tr, false>), rb, RANK_BLOCK, 0, st, dx + a, dy + a, dz + a, (u32)k, (u32)a, S, m->inv, m->dev, eff, touched, uncapped ? 1 : 0);
+            MMG_LAUNCH((k_insert_rank<Tr, false>), rb, RANK_BLOCK, 0, st, dx + a, dy + a, dz + a, (u32)k, (u32)a, S, m->inv, m->dev, eff, touched, seg_base,
+                       uncapped ? 1 : 0);
         const unsigned fb = persistent_blocks(m, k, 8, 8);
         MMG_LAUNCH((k_insert_commit<Tr>), fb, 256, 0, st, m->dev, touched, dx + a, dy + a, dz + a, (u32)a, S, m->inv, uncapped ? 0 : 1,
-                   m->kind == MMG_SPARSE_VOXEL ? 1 : 0);
+                   m->kind == MMG_SPARSE_VOXEL ? 1 : 0, seg_base, m->h_ctr);
         MMG_CUDA(cudaGetLastError());
-        if ((rc = read_counters(m, &c, st))) return rc;
+        // the commit kernel's last block has mirrored the counters into the pinned block: wait, no copy call
+        MMG_CUDA(cudaStreamSynchronize(st));
+        c        = *m->h_ctr;
+        seg_base = c.nseg;
         m->h_nvox_hi = c.nvox_hi;
         m->h_free_n  = c.free_n;
         a += k;

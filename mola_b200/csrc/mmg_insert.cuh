@@ -175,7 +175,7 @@ constexpr int RANK_BLOCK = 128;
 template <class Tr, bool MULTI>
 __global__ void __launch_bounds__(RANK_BLOCK)
     k_insert_rank(const float* __restrict__ xs, const float* __restrict__ ys, const float* __restrict__ zs, u32 n, u32 base, const ScanSet S, float inv,
-                  VoxelMapDev m, u32 eff_cap, u32* __restrict__ touched, int bbox_all)
+                  VoxelMapDev m, u32 eff_cap, u32* __restrict__ touched, u32 seg_base, int bbox_all)
 {
     constexpr int CAP   = Tr::CAP;
     const u32     i     = blockIdx.x * blockDim.x + threadIdx.x;
@@ -231,7 +231,7 @@ __global__ void __launch_bounds__(RANK_BLOCK)
             {
                 *reinterpret_cast<volatile u32*>(slot_w(m.pts + (size_t)vid * CAP + n0 + s)) = x;
                 alive = false;
-                if (s == 0) touched[atomicAdd(&m.ctr->nseg, 1u)] = vid;  // lists the voxel for k_insert_commit
+                if (s == 0) touched[atomicAdd(&m.ctr->nseg, 1u) - seg_base] = vid;  // lists the voxel for k_insert_commit
             }
             // the group that takes the last free slot tells later probes to skip the counter
             if (lane == first && pos < room && pos + (u32)__popc(want) >= room) atomicMax(&m.table[ent].cnt, (1u << RANK_CNT_BITS) | n0);
@@ -282,12 +282,13 @@ __global__ void __launch_bounds__(RANK_BLOCK)
 template <class Tr>
 __global__ void __launch_bounds__(256)
     k_insert_commit(VoxelMapDev m, const u32* __restrict__ touched, const float* __restrict__ xs, const float* __restrict__ ys,
-                    const float* __restrict__ zs, u32 base, ScanSet S, float inv, int bbox_accepted, int with_mean)
+                    const float* __restrict__ zs, u32 base, ScanSet S, float inv, int bbox_accepted, int with_mean, u32 seg_base,
+                    Counters* __restrict__ host_mirror)
 {
     constexpr int CAP    = Tr::CAP;
     const int     lane   = lane_id();
     const u32     nwarps = (gridDim.x * blockDim.x) >> 5;
-    const u32     nseg   = m.ctr->nseg;
+    const u32     nseg   = m.ctr->nseg - seg_base;  // nseg and oob run on from batch to batch: no memset launches in between
     for (u32 t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < nseg; t += nwarps)
     {
         const u32 vid  = touched[t];
@@ -336,6 +337,21 @@ __global__ void __launch_bounds__(256)
             Tr::to_index(p.y, inv, cy);
             Tr::to_index(p.z, inv, cz);
             publish_count<Tr>(m, vid, pack_key(cx, cy, cz), n0 + macc);
+        }
+    }
+    // the last block to finish mirrors the counters into pinned host memory: the host only has to wait for the stream
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        __threadfence();
+        if (atomicAdd(&m.ctr->done, 1u) == gridDim.x - 1)
+        {
+            m.ctr->done = 0;
+            __threadfence();
+            volatile u32*       dst = reinterpret_cast<volatile u32*>(host_mirror);
+            const volatile u32* src = reinterpret_cast<const volatile u32*>(m.ctr);
+            for (int k = 0; k < (int)(sizeof(Counters) / sizeof(u32)); k++) dst[k] = src[k];
+            __threadfence_system();
         }
     }
 }

@@ -21,7 +21,8 @@ struct Counters
     u32 nseg;      // segments of the current insert batch
     u32 bbox[6];   // ordered-uint min xyz / max xyz of points that passed the insertion checks
     u32 nlive_out; // export cursor
-    u32 pad[5];
+    u32 done;      // blocks of k_insert_commit that have finished (the last one mirrors the counters to the host)
+    u32 pad[4];
 };
 
 struct VoxelMapDev
