@@ -389,6 +389,15 @@ static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy,
             return (unsigned)((v == 64 || v == 128 || v == 256) ? v : 128);
         }();
         const unsigned nb = (unsigned)std::min<size_t>((nq + bs - 1) / bs, (size_t)m->num_sms * 64 * (256 / bs));
+        // tile order: a multiplier near grid / golden ratio, coprime to the grid (MMG_NN_PERMUTE=0: launch order)
+        static const bool permute = [] { const char* e = getenv("MMG_NN_PERMUTE"); return !e || atoi(e) != 0; }();
+        u32 perm = 1;
+        if (permute && nb > 8)
+        {
+            perm = (u32)(0.6180339887 * nb) | 1u;
+            auto gcd = [](u32 a, u32 b) { while (b) { const u32 t = a % b; a = b; b = t; } return a; };
+            while (gcd(perm, nb) != 1) perm += 2;
+        }
         // tuning knobs for the profiles: MMG_NN_VARIANT = <min blocks of 256 per SM: 5 (default) | 6 | 8><p for packed f32x2 math>
         static const int tv = [] {
             const char* e = getenv("MMG_NN_VARIANT");
@@ -398,12 +407,12 @@ static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy,
         }();
         switch (tv)
         {
-            case 1: MMG_LAUNCH((k_nn_single_pruned<Tr, 5, true>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
-            case 2: MMG_LAUNCH((k_nn_single_pruned<Tr, 6, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
-            case 3: MMG_LAUNCH((k_nn_single_pruned<Tr, 6, true>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
-            case 4: MMG_LAUNCH((k_nn_single_pruned<Tr, 8, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
-            case 5: MMG_LAUNCH((k_nn_single_pruned<Tr, 8, true>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
-            default: MMG_LAUNCH((k_nn_single_pruned<Tr, 5, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init);; break;
+            case 1: MMG_LAUNCH((k_nn_single_pruned<Tr, 5, true>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init, perm); break;
+            case 2: MMG_LAUNCH((k_nn_single_pruned<Tr, 6, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init, perm); break;
+            case 3: MMG_LAUNCH((k_nn_single_pruned<Tr, 6, true>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init, perm); break;
+            case 4: MMG_LAUNCH((k_nn_single_pruned<Tr, 8, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init, perm); break;
+            case 5: MMG_LAUNCH((k_nn_single_pruned<Tr, 8, true>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init, perm); break;
+            default: MMG_LAUNCH((k_nn_single_pruned<Tr, 5, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init, perm); break;
         }
     }
 }

@@ -256,14 +256,18 @@ __device__ __forceinline__ void nn_visit_cell(const VoxelMapDev& m, int b, int c
 template <class Tr, int MINB = 1, bool PACKED = false>
 __global__ void __launch_bounds__(256, MINB)
     k_nn_single_pruned(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride,
-                       PoseD pose, int use_pose, float inv, float vsize, QueryOut out, float bd_init)
+                       PoseD pose, int use_pose, float inv, float vsize, QueryOut out, float bd_init, u32 perm_mul)
 {
     // bd_init = +inf for nn_single_search; the matcher passes the largest float below its squared distance
     // threshold, which turns "d2 < threshold" into the initial branch-and-bound radius (mmg_match_batch)
     constexpr int CAP  = Tr::CAP;
     const int     lane = lane_id();
     // warp-uniform trip count: the coalesced result stores below shuffle across the whole warp
-    for (u32 q0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); q0 < n; q0 += gridDim.x * blockDim.x)
+    // Blocks take their 128-query tiles in a scattered order (tile = block * perm_mul mod grid, perm_mul coprime to the
+    // grid): a LiDAR batch has its heavy queries (dense near-field rings) in contiguous runs, and in launch order the
+    // last run would be the kernel's tail with most SMs idle (ncu: SM busy 200k..350k of 357k cycles without this).
+    const u32 tile = (u32)(((u64)blockIdx.x * perm_mul) % gridDim.x);
+    for (u32 q0 = tile * blockDim.x + (threadIdx.x & ~31u); q0 < n; q0 += gridDim.x * blockDim.x)
     {
         const u32  q     = q0 + (u32)lane;
         const bool valid = q < n;
