@@ -2,6 +2,9 @@
 // (include/mola_b200/mmg.h); reference behaviour is cited per method (mola_metric_maps/src/).
 #include "GpuMetricMaps.h"
 
+#include <array>
+#include <map>
+
 #include <mrpt/core/exceptions.h>
 #include <mrpt/obs/CObservation2DRangeScan.h>
 #include <mrpt/obs/CObservation3DRangeScan.h>
@@ -569,16 +572,145 @@ void SparseVoxelPointCloud::TLikelihoodOptions::dumpToTextStream(std::ostream& o
     LOADABLEOPTS_DUMP_VAR(decimation, int);
     LOADABLEOPTS_DUMP_VAR(match_mean, bool);
 }
-// The reference archives embed MRPT's CSimplePointsMap stream (SparseVoxelPointCloud.cpp:111-189,
-// SparseTreesPointCloud.cpp:111-167), whose format lives in MRPT and is absent here.
-uint8_t SparseVoxelPointCloud::serializeGetVersion() const { return 0; }
-void    SparseVoxelPointCloud::serializeTo(mrpt::serialization::CArchive&) const
+// Option blocks: SparseVoxelPointCloud.cpp:880-960.
+static void check_opts_version(int8_t version)
 {
-    THROW_EXCEPTION("SparseVoxelPointCloud (GPU): serialization needs MRPT's CSimplePointsMap archive format; not available in this build");
+    if (version != 0) MRPT_THROW_UNKNOWN_SERIALIZATION_VERSION(version);
 }
-void SparseVoxelPointCloud::serializeFrom(mrpt::serialization::CArchive&, uint8_t)
+void SparseVoxelPointCloud::TInsertionOptions::writeToStream(mrpt::serialization::CArchive& out) const
 {
-    THROW_EXCEPTION("SparseVoxelPointCloud (GPU): serialization needs MRPT's CSimplePointsMap archive format; not available in this build");
+    const int8_t version = 0;
+    out << version << max_points_per_voxel;
+}
+void SparseVoxelPointCloud::TInsertionOptions::readFromStream(mrpt::serialization::CArchive& in)
+{
+    int8_t version;
+    in >> version;
+    check_opts_version(version);
+    in >> max_points_per_voxel;
+}
+void SparseVoxelPointCloud::TLikelihoodOptions::writeToStream(mrpt::serialization::CArchive& out) const
+{
+    const int8_t version = 0;
+    out << version << sigma_dist << max_corr_distance << decimation << match_mean;
+}
+void SparseVoxelPointCloud::TLikelihoodOptions::readFromStream(mrpt::serialization::CArchive& in)
+{
+    int8_t version;
+    in >> version;
+    check_opts_version(version);
+    in >> sigma_dist >> max_corr_distance >> decimation >> match_mean;
+}
+void SparseVoxelPointCloud::TRenderOptions::writeToStream(mrpt::serialization::CArchive& out) const
+{
+    const int8_t version = 0;
+    out << version << point_size << show_mean_only << show_inner_grid_boxes << color << colormap << recolorizeByCoordinateIndex;
+}
+void SparseVoxelPointCloud::TRenderOptions::readFromStream(mrpt::serialization::CArchive& in)
+{
+    int8_t version;
+    in >> version;
+    check_opts_version(version);
+    in >> point_size >> show_mean_only >> show_inner_grid_boxes >> color >> colormap >> recolorizeByCoordinateIndex;
+}
+
+// Serialization v0 in the reference's layout (SparseVoxelPointCloud.cpp:111-189): inner-grid bit count, voxel size, the
+// three option blocks, then per 32^3 block its outer index, the block's points as an embedded CSimplePointsMap object
+// (written by MRPT's own operator<<, so the point-map format is whatever the linked MRPT defines) and, for each of the
+// 32768 cells, a uint16 count and the uint32 indices of the cell's points inside that block. The reference keeps a
+// block's points in insertion order across cells; the device map only knows the order inside a voxel, so blocks are
+// written cell by cell (a reader gets the same voxels with the same per-voxel point order). Blocks go out in
+// lexicographic (cx, cy, cz) order.
+uint8_t SparseVoxelPointCloud::serializeGetVersion() const { return 0; }
+void    SparseVoxelPointCloud::serializeTo(mrpt::serialization::CArchive& out) const
+{
+    constexpr uint32_t INNER_BITS = 5, INNER_MASK = (1u << INNER_BITS) - 1u, CELLS = 1u << (3 * INNER_BITS);
+    out << INNER_BITS << voxelSize();
+    insertionOptions.writeToStream(out);
+    likelihoodOptions.writeToStream(out);
+    renderOptions.writeToStream(out);
+    std::vector<int32_t>               k;
+    std::vector<uint32_t>              c;
+    std::vector<mrpt::math::TPoint3Df> p;
+    uint32_t                           cap = 0;
+    exportVoxels(k, c, p, cap);
+    // outer index (g2o: idx & ~31, SparseVoxelPointCloud.h:84-90) -> voxels of the block as (plain inner index, voxel)
+    std::map<std::array<int32_t, 3>, std::vector<std::pair<uint32_t, uint32_t>>> blocks;
+    for (size_t v = 0; v < c.size(); v++)
+    {
+        if (!c[v]) continue;
+        const int32_t  gx = k[3 * v], gy = k[3 * v + 1], gz = k[3 * v + 2];
+        const uint32_t plain = ((uint32_t)gx & INNER_MASK) | (((uint32_t)gy & INNER_MASK) << INNER_BITS) | (((uint32_t)gz & INNER_MASK) << (2 * INNER_BITS));
+        blocks[{gx & ~(int32_t)INNER_MASK, gy & ~(int32_t)INNER_MASK, gz & ~(int32_t)INNER_MASK}].emplace_back(plain, (uint32_t)v);
+    }
+    out.WriteAs<uint32_t>(blocks.size());
+    std::vector<uint32_t> first(CELLS), count(CELLS);
+    for (auto& kv : blocks)
+    {
+        out << kv.first[0] << kv.first[1] << kv.first[2];
+        std::sort(kv.second.begin(), kv.second.end());
+        mrpt::maps::CSimplePointsMap pts;
+        std::fill(count.begin(), count.end(), 0u);
+        uint32_t next = 0;
+        for (const auto& cell : kv.second)
+        {
+            first[cell.first] = next, count[cell.first] = c[cell.second];
+            for (uint32_t j = 0; j < c[cell.second]; j++)
+            {
+                const auto& q = p[(size_t)cell.second * cap + j];
+                pts.insertPointFast(q.x, q.y, q.z);
+            }
+            next += c[cell.second];
+        }
+        out << pts;
+        for (uint32_t i = 0; i < CELLS; i++)
+        {
+            out.WriteAs<uint16_t>(count[i]);
+            for (uint32_t j = 0; j < count[i]; j++) out.WriteAs<uint32_t>(first[i] + j);
+        }
+    }
+}
+void SparseVoxelPointCloud::serializeFrom(mrpt::serialization::CArchive& in, uint8_t version)
+{
+    if (version != 0) MRPT_THROW_UNKNOWN_SERIALIZATION_VERSION(version);
+    constexpr uint32_t INNER_BITS = 5, CELLS = 1u << (3 * INNER_BITS);
+    const auto         bits = in.ReadAs<uint32_t>();
+    ASSERT_EQUAL_(bits, INNER_BITS);
+    float vs;
+    in >> vs;
+    setVoxelProperties(vs);  // clears
+    insertionOptions.readFromStream(in);
+    likelihoodOptions.readFromStream(in);
+    renderOptions.readFromStream(in);
+    // The reference restores each cell's index list verbatim (and leaves the cells' running means at zero, .cpp:166-181);
+    // here the cells' points are re-filed in list order with the cap switched off, which gives the same voxels and
+    // per-voxel order, with the means recomputed.
+    const auto         nGrids = in.ReadAs<uint32_t>();
+    std::vector<float> xs, ys, zs;
+    for (uint32_t g = 0; g < nGrids; g++)
+    {
+        int32_t ox, oy, oz;
+        in >> ox >> oy >> oz;
+        mrpt::maps::CSimplePointsMap pts;
+        in >> pts;
+        for (uint32_t i = 0; i < CELLS; i++)
+        {
+            const auto n = in.ReadAs<uint16_t>();
+            for (uint16_t j = 0; j < n; j++)
+            {
+                const auto idx = in.ReadAs<uint32_t>();
+                ASSERT_LT_(idx, pts.size());
+                float x, y, z;
+                pts.getPointFast(idx, x, y, z);
+                xs.push_back(x), ys.push_back(y), zs.push_back(z);
+            }
+        }
+    }
+    const TInsertionOptions keep = insertionOptions;
+    insertionOptions.max_points_per_voxel = 0;
+    insertPointCloud(xs.data(), ys.data(), zs.data(), xs.size(), std::nullopt, false);
+    insertionOptions = keep;
+    check(mmg_invalidate_bbox(h_));  // cached_.reset() (.cpp:188)
 }
 SparseVoxelPointCloud::TMapDefinition::TMapDefinition() = default;
 void SparseVoxelPointCloud::TMapDefinition::loadFromConfigFile_map_specific(const mrpt::config::CConfigFileBase& s, const std::string& sectionPrefix)
@@ -648,14 +780,108 @@ void SparseTreesPointCloud::TLikelihoodOptions::dumpToTextStream(std::ostream& o
     LOADABLEOPTS_DUMP_VAR(max_corr_distance, double);
     LOADABLEOPTS_DUMP_VAR(decimation, int);
 }
-uint8_t SparseTreesPointCloud::serializeGetVersion() const { return 0; }
-void    SparseTreesPointCloud::serializeTo(mrpt::serialization::CArchive&) const
+// Option blocks: SparseTreesPointCloud.cpp:770-850.
+void SparseTreesPointCloud::TInsertionOptions::writeToStream(mrpt::serialization::CArchive& out) const
 {
-    THROW_EXCEPTION("SparseTreesPointCloud (GPU): serialization needs MRPT's CSimplePointsMap archive format; not available in this build");
+    const int8_t version = 0;
+    out << version << minimum_points_clearance << remove_submaps_farther_than;
 }
-void SparseTreesPointCloud::serializeFrom(mrpt::serialization::CArchive&, uint8_t)
+void SparseTreesPointCloud::TInsertionOptions::readFromStream(mrpt::serialization::CArchive& in)
 {
-    THROW_EXCEPTION("SparseTreesPointCloud (GPU): serialization needs MRPT's CSimplePointsMap archive format; not available in this build");
+    int8_t version;
+    in >> version;
+    check_opts_version(version);
+    in >> minimum_points_clearance >> remove_submaps_farther_than;
+}
+void SparseTreesPointCloud::TLikelihoodOptions::writeToStream(mrpt::serialization::CArchive& out) const
+{
+    const int8_t version = 0;
+    out << version << sigma_dist << max_corr_distance << decimation;
+}
+void SparseTreesPointCloud::TLikelihoodOptions::readFromStream(mrpt::serialization::CArchive& in)
+{
+    int8_t version;
+    in >> version;
+    check_opts_version(version);
+    in >> sigma_dist >> max_corr_distance >> decimation;
+}
+void SparseTreesPointCloud::TRenderOptions::writeToStream(mrpt::serialization::CArchive& out) const
+{
+    const int8_t version = 0;
+    out << version << point_size << show_inner_grid_boxes << color << colormap << recolorizeByCoordinateIndex;
+}
+void SparseTreesPointCloud::TRenderOptions::readFromStream(mrpt::serialization::CArchive& in)
+{
+    int8_t version;
+    in >> version;
+    check_opts_version(version);
+    in >> point_size >> show_inner_grid_boxes >> color >> colormap >> recolorizeByCoordinateIndex;
+}
+
+// Serialization v0 in the reference's layout (SparseTreesPointCloud.cpp:111-167): the id bit count (uint8 20), grid size,
+// the three option blocks, then per block its index and its points as an embedded CSimplePointsMap object in
+// block-local index order (the ids nn_*_search returns survive the round trip). Blocks go out in lexicographic order.
+uint8_t SparseTreesPointCloud::serializeGetVersion() const { return 0; }
+void    SparseTreesPointCloud::serializeTo(mrpt::serialization::CArchive& out) const
+{
+    const uint8_t id_bits = 20;  // GLOBAL_ID_SUBVOXEL_BITCOUNT, SparseTreesPointCloud.h:58
+    out << id_bits << gridSize();
+    insertionOptions.writeToStream(out);
+    likelihoodOptions.writeToStream(out);
+    renderOptions.writeToStream(out);
+    std::vector<int32_t>               k;
+    std::vector<uint32_t>              c;
+    std::vector<mrpt::math::TPoint3Df> p;
+    uint32_t                           cap = 0;
+    exportVoxels(k, c, p, cap);
+    std::map<std::array<int32_t, 3>, size_t> blocks;
+    for (size_t v = 0; v < c.size(); v++) blocks[{k[3 * v], k[3 * v + 1], k[3 * v + 2]}] = v;
+    out.WriteAs<uint32_t>(blocks.size());
+    for (const auto& kv : blocks)
+    {
+        out << kv.first[0] << kv.first[1] << kv.first[2];
+        mrpt::maps::CSimplePointsMap pts;
+        pts.reserve(c[kv.second]);
+        for (uint32_t j = 0; j < c[kv.second]; j++)
+        {
+            const auto& q = p[kv.second * (size_t)cap + j];
+            pts.insertPointFast(q.x, q.y, q.z);
+        }
+        out << pts;
+    }
+}
+void SparseTreesPointCloud::serializeFrom(mrpt::serialization::CArchive& in, uint8_t version)
+{
+    if (version != 0) MRPT_THROW_UNKNOWN_SERIALIZATION_VERSION(version);
+    const auto bits = in.ReadAs<uint8_t>();
+    ASSERT_EQUAL_(bits, 20);
+    float gs;
+    in >> gs;
+    setGridProperties(gs);  // clears
+    insertionOptions.readFromStream(in);
+    likelihoodOptions.readFromStream(in);
+    renderOptions.readFromStream(in);
+    // All blocks go in as ONE batch, block after block and each block's points in stored order: the clearance test only
+    // looks at the map as it was before the batch (empty here, .cpp:916-959), so every point is accepted, and a block's
+    // local indices are assigned in input order, so the ids nn_*_search returns are preserved. The archive's block
+    // index is implied by the points themselves (coordToOuterIdx, .h:70-77).
+    const auto         nGrids = in.ReadAs<uint32_t>();
+    std::vector<float> xs, ys, zs;
+    for (uint32_t g = 0; g < nGrids; g++)
+    {
+        int32_t ox, oy, oz;
+        in >> ox >> oy >> oz;
+        mrpt::maps::CSimplePointsMap pts;
+        in >> pts;
+        for (size_t i = 0; i < pts.size(); i++)
+        {
+            float x, y, z;
+            pts.getPointFast(i, x, y, z);
+            xs.push_back(x), ys.push_back(y), zs.push_back(z);
+        }
+    }
+    insertPointCloud(xs.data(), ys.data(), zs.data(), xs.size(), std::nullopt, false);
+    check(mmg_invalidate_bbox(h_));  // cached_.reset() (.cpp:166)
 }
 SparseTreesPointCloud::TMapDefinition::TMapDefinition() = default;
 void SparseTreesPointCloud::TMapDefinition::loadFromConfigFile_map_specific(const mrpt::config::CConfigFileBase& s, const std::string& sectionPrefix)

@@ -229,19 +229,36 @@ class SparseVoxelPointCloud : public GpuPointMapBase
     {
         void loadFromConfigFile(const mrpt::config::CConfigFileBase& source, const std::string& section) override;
         void dumpToTextStream(std::ostream& out) const override;
+        void writeToStream(mrpt::serialization::CArchive& out) const;
+        void readFromStream(mrpt::serialization::CArchive& in);
         uint32_t max_points_per_voxel = 0;
     };
     struct TLikelihoodOptions : public mrpt::config::CLoadableOptions
     {
         void loadFromConfigFile(const mrpt::config::CConfigFileBase& source, const std::string& section) override;
         void dumpToTextStream(std::ostream& out) const override;
+        void writeToStream(mrpt::serialization::CArchive& out) const;
+        void readFromStream(mrpt::serialization::CArchive& in);
         double   sigma_dist        = 0.5;
         double   max_corr_distance = 1.0;
         uint32_t decimation        = 10;
         bool     match_mean        = false;
     };
+    /** Carried through the archive only (SparseVoxelPointCloud.h:470-494); nothing is rendered here. */
+    struct TRenderOptions
+    {
+        void writeToStream(mrpt::serialization::CArchive& out) const;
+        void readFromStream(mrpt::serialization::CArchive& in);
+        float              point_size            = 1.0f;
+        bool               show_mean_only        = true;
+        bool               show_inner_grid_boxes = false;
+        mrpt::img::TColorf color{.0f, .0f, 1.0f};
+        int8_t             colormap                    = 2;  // mrpt::img::cmHOT
+        uint8_t            recolorizeByCoordinateIndex = 2;
+    };
     TInsertionOptions  insertionOptions;
     TLikelihoodOptions likelihoodOptions;
+    TRenderOptions     renderOptions;
 
     MAP_DEFINITION_START(SparseVoxelPointCloud)
     float              voxel_size = 0.20f;
@@ -269,6 +286,8 @@ class SparseTreesPointCloud : public GpuPointMapBase
     {
         void loadFromConfigFile(const mrpt::config::CConfigFileBase& source, const std::string& section) override;
         void dumpToTextStream(std::ostream& out) const override;
+        void writeToStream(mrpt::serialization::CArchive& out) const;
+        void readFromStream(mrpt::serialization::CArchive& in);
         float minimum_points_clearance    = 0.20f;
         float remove_submaps_farther_than = .0f;
     };
@@ -276,12 +295,26 @@ class SparseTreesPointCloud : public GpuPointMapBase
     {
         void loadFromConfigFile(const mrpt::config::CConfigFileBase& source, const std::string& section) override;
         void dumpToTextStream(std::ostream& out) const override;
+        void writeToStream(mrpt::serialization::CArchive& out) const;
+        void readFromStream(mrpt::serialization::CArchive& in);
         double   sigma_dist        = 0.5;
         double   max_corr_distance = 1.0;
         uint32_t decimation        = 10;
     };
+    /** Carried through the archive only (SparseTreesPointCloud.h:388-406); nothing is rendered here. */
+    struct TRenderOptions
+    {
+        void writeToStream(mrpt::serialization::CArchive& out) const;
+        void readFromStream(mrpt::serialization::CArchive& in);
+        float              point_size            = 1.0f;
+        bool               show_inner_grid_boxes = false;
+        mrpt::img::TColorf color{.0f, .0f, 1.0f};
+        int8_t             colormap                    = 2;  // mrpt::img::cmHOT
+        uint8_t            recolorizeByCoordinateIndex = 2;
+    };
     TInsertionOptions  insertionOptions;
     TLikelihoodOptions likelihoodOptions;
+    TRenderOptions     renderOptions;
 
     MAP_DEFINITION_START(SparseTreesPointCloud)
     float              grid_size = 10.0f;

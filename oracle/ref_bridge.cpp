@@ -151,6 +151,37 @@ void*       mmo_create(int kind, const mmo_params* p)
     return H;
 }
 void mmo_destroy(void* h) { delete (Handle*)h; }
+// Archives written / read by the reference classes' own serializeTo / serializeFrom (through the shim's CArchive):
+// the byte streams the C++ host classes of mola_b200/host must be able to read and produce.
+// Only in this library (the port has no archive code). mmo_ref_serialize returns the archive size; it fills `out`
+// when cap is large enough.
+size_t mmo_ref_serialize(void* h, uint8_t* out, size_t cap)
+{
+    auto*                         H = (Handle*)h;
+    mrpt::serialization::CArchive ar;
+    if (H->kind == 0) ar << *H->hv;
+    else if (H->kind == 1) ar << *H->sv;
+    else ar << *H->st;
+    if (out && cap >= ar.buf.size()) std::memcpy(out, ar.buf.data(), ar.buf.size());
+    return ar.buf.size();
+}
+int mmo_ref_deserialize(void* h, const uint8_t* buf, size_t n)
+{
+    auto* H = (Handle*)h;
+    try
+    {
+        mrpt::serialization::CArchive ar;
+        ar.buf.assign(buf, buf + n);
+        if (H->kind == 0) ar >> *H->hv;
+        else if (H->kind == 1) ar >> *H->sv;
+        else ar >> *H->st;
+        return ar.rpos == ar.buf.size() ? 0 : -2;
+    }
+    catch (const std::exception&)
+    {
+        return -1;
+    }
+}
 void mmo_clear(void* h) { ((Handle*)h)->base()->clear(); }
 void mmo_set_params(void* h, const mmo_params* p) { ((Handle*)h)->apply(*p, false); }
 int  mmo_is_empty(void* h) { return ((Handle*)h)->base()->isEmpty() ? 1 : 0; }

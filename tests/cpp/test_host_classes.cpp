@@ -18,6 +18,7 @@ namespace mg = MOLA_B200_NAMESPACE;
 using mrpt::math::TPoint3Df;
 
 static int g_fail = 0;
+static int g_archive_cross_checks = 0;
 #define CHECK(c)                                                     \
     do {                                                             \
         if (!(c))                                                    \
@@ -57,6 +58,9 @@ struct Oracle
     decltype(&mmo_num_points)    num_points;
     decltype(&mmo_row_capacity)  row_capacity;
     decltype(&mmo_export)        export_;
+    // reference library only (nullptr with the port): archives of the reference classes themselves
+    size_t (*ref_serialize)(void*, uint8_t*, size_t)        = nullptr;
+    int (*ref_deserialize)(void*, const uint8_t*, size_t)   = nullptr;
     explicit Oracle(const char* path)
     {
         h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
@@ -69,6 +73,7 @@ struct Oracle
         S(create, "mmo_create"), S(destroy, "mmo_destroy"), S(insert, "mmo_insert"), S(nn_single, "mmo_nn_single"), S(nn_multi, "mmo_nn_multi");
         S(nn_radius, "mmo_nn_radius"), S(nn_radius_fetch, "mmo_nn_radius_fetch"), S(likelihood, "mmo_likelihood"), S(bbox, "mmo_bbox");
         S(num_voxels, "mmo_num_voxels"), S(num_points, "mmo_num_points"), S(row_capacity, "mmo_row_capacity"), S(export_, "mmo_export");
+        S(ref_serialize, "mmo_ref_serialize"), S(ref_deserialize, "mmo_ref_deserialize");
 #undef S
     }
 };
@@ -330,6 +335,47 @@ static void run_case(Oracle& O, const Case& c)
         uint64_t              id;
         CHECK_THROWS((void)nn->nn_single_search(q2, r2, d, id));
     }
+    if (O.ref_serialize && O.ref_deserialize)
+    {   // archives cross the boundary both ways: the reference class reads what the GPU class wrote, and vice versa
+        mrpt::serialization::CArchive ar;
+        ar << *m;
+        void* o2 = O.create(c.kind, &c.prm);
+        CHECK(O.ref_deserialize(o2, ar.buf.data(), ar.buf.size()) == 0);
+        std::vector<int32_t>  gk;
+        std::vector<uint32_t> gc;
+        std::vector<float>    gp;
+        uint32_t              cap = 0;
+        sorted_export(*m, gk, gc, gp, cap);
+        const size_t V = O.num_voxels(o2);
+        CHECK(V == gc.size() && O.num_points(o2) == m->numPoints() && O.row_capacity(o2) == cap);
+        if (V == gc.size() && O.row_capacity(o2) == cap)
+        {
+            std::vector<int32_t>  ok(3 * V);
+            std::vector<uint32_t> oc(V);
+            std::vector<float>    op(V * cap * 3);
+            if (V) O.export_(o2, ok.data(), oc.data(), op.data());
+            CHECK(gk == ok && gc == oc && same_bits(gp.data(), op.data(), op.size()));
+        }
+        O.destroy(o2);
+        // the other way round: the reference's archive of its own map, read by the GPU class
+        std::vector<uint8_t> bytes(O.ref_serialize(o, nullptr, 0));
+        CHECK(O.ref_serialize(o, bytes.data(), bytes.size()) == bytes.size());
+        mrpt::serialization::CArchive in;
+        in.buf = bytes;
+        std::unique_ptr<mg::GpuPointMapBase> back;
+        if (c.kind == 0) back.reset(new mg::HashedVoxelPointCloud(1.0f));
+        else if (c.kind == 1) back.reset(new mg::SparseVoxelPointCloud(1.0f));
+        else back.reset(new mg::SparseTreesPointCloud(1.0f));
+        in >> *back;
+        CHECK(in.rpos == in.buf.size());
+        std::vector<int32_t>  bk;
+        std::vector<uint32_t> bc;
+        std::vector<float>    bp;
+        uint32_t              bcap = 0;
+        sorted_export(*back, bk, bc, bp, bcap);
+        CHECK(bk == gk && bc == gc && bcap == cap && bp.size() == gp.size() && same_bits(bp.data(), gp.data(), gp.size()));
+        g_archive_cross_checks++;
+    }
     // value semantics: a copy is deep
     if (c.kind == 0)
     {
@@ -353,6 +399,57 @@ static void run_case(Oracle& O, const Case& c)
         sorted_export(back, k2, c2, p2, cap2);
         CHECK(k1 == k2 && c1 == c2 && p1.size() == p2.size() && same_bits(p1.data(), p2.data(), p1.size()));
         CHECK(back.getAsSimplePointsMap()->size() == back.numPoints());
+    }
+    else
+    {   // serialization v0 round trip of the two block-structured maps (reference layout: SparseVoxelPointCloud.cpp:111-189,
+        // SparseTreesPointCloud.cpp:111-167): same voxels / blocks, same per-voxel (per-block) point order, same options
+        mrpt::serialization::CArchive ar;
+        ar << *m;
+        std::unique_ptr<mg::GpuPointMapBase> back;
+        if (c.kind == 1) back.reset(new mg::SparseVoxelPointCloud(1.0f));
+        else back.reset(new mg::SparseTreesPointCloud(1.0f));
+        ar >> *back;
+        CHECK(ar.rpos == ar.buf.size());
+        CHECK(back->numPoints() == m->numPoints());
+        std::vector<int32_t>  k1, k2;
+        std::vector<uint32_t> c1, c2;
+        std::vector<float>    p1, p2;
+        uint32_t              cap1, cap2;
+        sorted_export(*m, k1, c1, p1, cap1);
+        sorted_export(*back, k2, c2, p2, cap2);
+        CHECK(k1 == k2 && c1 == c2 && cap1 == cap2 && p1.size() == p2.size() && same_bits(p1.data(), p2.data(), p1.size()));
+        if (c.kind == 1)
+        {
+            auto* a = dynamic_cast<mg::SparseVoxelPointCloud*>(m);
+            auto* b = dynamic_cast<mg::SparseVoxelPointCloud*>(back.get());
+            CHECK(b->voxelSize() == a->voxelSize());
+            CHECK(b->insertionOptions.max_points_per_voxel == a->insertionOptions.max_points_per_voxel);
+            CHECK(b->likelihoodOptions.match_mean == a->likelihoodOptions.match_mean && b->likelihoodOptions.decimation == a->likelihoodOptions.decimation);
+        }
+        else
+        {
+            auto* a = dynamic_cast<mg::SparseTreesPointCloud*>(m);
+            auto* b = dynamic_cast<mg::SparseTreesPointCloud*>(back.get());
+            CHECK(b->gridSize() == a->gridSize());
+            CHECK(b->insertionOptions.minimum_points_clearance == a->insertionOptions.minimum_points_clearance);
+            CHECK(b->insertionOptions.remove_submaps_farther_than == a->insertionOptions.remove_submaps_farther_than);
+            // block-local point indices survive: the ids nn_single_search returns are the same
+            mg::NNBatchResult r1, r2;
+            m->nn_single_search_batch(qx.data(), qy.data(), qz.data(), nq, r1);
+            back->nn_single_search_batch(qx.data(), qy.data(), qz.data(), nq, r2);
+            CHECK(r1.found == r2.found && r1.ids == r2.ids && same_bits(r1.dist_sqr.data(), r2.dist_sqr.data(), nq));
+        }
+        // radius search (all hits, then the 3 nearest) gives the same answers on the restored map
+        for (size_t maxp : {size_t(0), size_t(3)})
+            for (size_t i = 0; i < nq; i += 7)
+            {
+                std::vector<TPoint3Df> ra, rb;
+                std::vector<float>     da, db;
+                std::vector<uint64_t>  ia, ib;
+                nn->nn_radius_search(TPoint3Df(qx[i], qy[i], qz[i]), 0.8f * 0.8f, ra, da, ia, maxp);
+                back->nn_radius_search(TPoint3Df(qx[i], qy[i], qz[i]), 0.8f * 0.8f, rb, db, ib, maxp);
+                CHECK(ia == ib && da.size() == db.size() && (da.empty() || same_bits(da.data(), db.data(), da.size())));
+            }
     }
     O.destroy(o);
 }
@@ -388,6 +485,7 @@ int main(int argc, char** argv)
         std::printf("EXCEPTION: %s\n", e.what());
         return 1;
     }
+    std::printf("archives cross-checked with the reference classes: %d cases\n", g_archive_cross_checks);
     std::printf(g_fail ? "%d CHECKS FAILED\n" : "ALL OK\n", g_fail);
     return g_fail ? 1 : 0;
 }

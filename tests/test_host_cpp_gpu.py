@@ -36,3 +36,5 @@ def test_host_classes_against_oracle(built):
     r = subprocess.run([exe, ora], capture_output=True, text=True, timeout=600)
     print(r.stdout[-3000:], r.stderr[-2000:])
     assert r.returncode == 0 and "ALL OK" in r.stdout
+    if mmo.have_reference():  # serializeTo/From of all three maps against the reference classes' own archives
+        assert "archives cross-checked with the reference classes: 6 cases" in r.stdout
