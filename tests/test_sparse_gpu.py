@@ -213,3 +213,28 @@ def test_sparse_trees_match_points(built):
     assert 0 < idx.size < q[0].size
     assert np.array_equal(idx, np.nonzero(keep)[0].astype(np.uint32)) and np.array_equal(ids, oi[keep])
     assert np.array_equal(bits(d2), bits(od[keep])) and np.array_equal(bits(pts), bits(op[keep]))
+
+
+@pytest.mark.parametrize("kind,size,cap", [(0, 1.0, 0), (0, 1.0, 5), (1, 1.0, 0), (1, 1.0, 7)])
+def test_insert_hot_voxels_out_of_order(built, kind, size, cap):
+    """The free-slot set of k_insert_rank under the heaviest contention: 1.5 M points of 27 voxels in one batch, so every
+    voxel is hit by thousands of warps at once and the earliest points of a voxel routinely arrive after later ones have
+    taken its slots (replace-the-minimum path, published bounds, retries). Three batches: the first leaves rows partially
+    filled, the second fills them, the third must be rejected by the probe alone. Hashed (cap 32) and SparseVoxel
+    (cap 16, running means), hard cap and max_points_per_voxel."""
+    rng = np.random.default_rng(11 + kind + cap)
+    opts = dict(max_points_per_voxel=cap) if cap else dict()
+    g, o = _pair(kind, size, **opts)
+    for n in (60, 1_500_000, 300_000):
+        cells = rng.integers(0, 3, size=(n, 3)).astype(np.float32)
+        p = cells + rng.random((n, 3), dtype=np.float32) * np.float32(0.8) + np.float32(0.1)
+        if kind == 1:
+            p -= np.float32(0.5)  # SparseVoxel cells are centred on k * size
+        x, y, z = (np.ascontiguousarray(p[:, a]) for a in range(3))
+        g.insert(x, y, z)
+        o.insert(x, y, z)
+        _same_export(g, o)
+    if kind == 1:
+        gm, _ = g.voxel_stats()
+        om, _ = o.voxel_stats()
+        assert np.array_equal(bits(gm), bits(om))
