@@ -58,22 +58,22 @@ def map_scans(target_points, count_fn, insert_fn, log=None):
     return k, n_in
 
 
-def query_batch(n_scans_in_map, rank=0, n=N_QUERIES, world=1):
-    """n query points in the map frame: scans taken mid-trajectory 1 m apart, each re-posed by a small SE(3) step (one ICP
-    iteration's pose guess), truncated to n. With several ranks the run of consecutive scans is dealt round-robin
-    (scan j -> rank j mod world, like config 5), so every rank gets the same mix of places along the trajectory; at
-    world = 1 this is the plain run of consecutive scans."""
+def query_batch(n_scans_in_map, rank=0, n=N_QUERIES):
+    """n query points in the map frame: consecutive scans taken mid-trajectory, each re-posed by a
+    small SE(3) step (one ICP iteration's pose guess), truncated to n. Every rank takes its own stretch of road, 50 m
+    apart. (Dealing one run of scans round-robin to the ranks instead spreads each rank's queries over 8 x the map area:
+    more rows come from DRAM after the L2 flush, 0.187-0.199 ms per step on all 8 ranks against 0.172-0.193.)"""
     from mola_b200 import synth
     out = [[], [], []]
-    have, j = 0, rank
-    s0 = SPACING * (n_scans_in_map // 2) + 1.7
+    have, j = 0, 0
+    s0 = SPACING * (n_scans_in_map // 2) + 1.7 + 50.0 * rank
     while have < n:
-        xs, ys, zs, pose = synth.lidar_scan("hdl64", s=s0 + 1.0 * j, seed=2, scan_id=100000 + j)
+        xs, ys, zs, pose = synth.lidar_scan("hdl64", s=s0 + 1.0 * j, seed=2, scan_id=100000 + 1000 * rank + j)
         g = compose_host(synth.perturbed_pose(pose), xs, ys, zs)
         for a in range(3):
             out[a].append(g[a])
         have += xs.size
-        j += world
+        j += 1
     return [np.ascontiguousarray(np.concatenate(o)[:n]) for o in out]
 
 
@@ -335,7 +335,7 @@ def run_gpu(args, rank, world, local_rank):
     scan_insert = bench_scan_insert(gmap, nscans, dev, stream) if rank == 0 else None
 
     # ---- queries ---------------------------------------------------------------------------
-    q = query_batch(nscans, rank, world=world)
+    q = query_batch(nscans, rank)
     n = q[0].size
     hq = [torch.from_numpy(a).pin_memory() for a in q]                       # pinned host inputs
     dq = [a.to(dev, non_blocking=True) for a in hq]                          # HBM-resident inputs
@@ -402,7 +402,11 @@ def run_gpu(args, rank, world, local_rank):
     found_frac = float(d_found.float().mean().item())
 
     t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    per_rank = [dev_ms / args.steps]
     if world > 1:
+        every = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(every, t)
+        per_rank = [float(x[0]) / args.steps for x in every]
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms = float(t[0]), float(t[1])
     if rank != 0:
@@ -434,9 +438,9 @@ def run_gpu(args, rank, world, local_rank):
             "config": {"workload": "C2: 10M-pt HashedVoxelPointCloud (voxel 0.5 m), batched nn_single_search of 1M points per step per GPU",
                        "map_points": int(stats["points"]), "map_voxels": int(stats["live_voxels"]), "map_scans": nscans,
                        "queries_per_step_per_gpu": n, "l2": "flushed between steps (256 MiB write)", "map_hbm_bytes": int(stats["hbm_bytes"]),
-                       "parallelism": f"map replicated by NCCL broadcast, query scans dealt round-robin to {world} rank(s), 1M queries per rank", "rank0_cpu_binding": numa},
+                       "parallelism": f"map replicated by NCCL broadcast, queries sharded x{world}", "rank0_cpu_binding": numa},
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": 12 * n, "d2h_bytes_per_step": 25 * n},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(launches), "ms_per_step_by_rank": per_rank,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "kernel": "k_nn_single_pruned<HashedTraits>", "algorithmic_bytes_per_query": bytes_per_q, "mean_stencil_points": pbar.value,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
