@@ -129,10 +129,14 @@ constexpr u32 RANK_CNT_BITS  = 6;
 constexpr u32 RANK_CODE_MASK = (1u << 26) - 1;
 constexpr u32 RANK_MAX_CHUNK = 1u << 25;  // chunk-local indices stay below 2^26 - 1, so a 26-bit code is never 0
 
-// find-or-insert that also returns the entry's count word and position. One 16-byte L2 load (ld.cg) per probe returns
-// key, row id and count word together. A voxel created by THIS batch has count 0 until k_insert_commit runs, so a reader
-// that has to wait for the creator's row id (or still sees the 0xFFFFFFFF of the never-used entry) knows the word is 0.
-__device__ __forceinline__ u32 find_or_insert_cnt(const VoxelMapDev& m, u64 key, u32& cntword, u32& ent)
+// Probe for the insert kernel. One 16-byte L2 load (ld.cg) per probe returns key, row id and count word together.
+// Outcomes: PROBE_FOUND (row id and count word valid), PROBE_CLAIMED (this thread won the empty entry: it still has to
+// get a row and publish it), PROBE_PENDING (another thread of this batch won it and has not published the row yet).
+// Nothing waits in here: rows are allocated and published after the loop with one counter update per warp, and only
+// then do the pending lanes wait (a creator that had to wait for its own warp's pending lanes first could be waited on
+// in a circle). A voxel created by THIS batch has count 0 until k_insert_commit runs.
+enum { PROBE_NONE = 0, PROBE_FOUND, PROBE_CLAIMED, PROBE_PENDING };
+__device__ __forceinline__ int probe_or_claim(const VoxelMapDev& m, u64 key, u32& vid, u32& cntword, u32& ent)
 {
     u64 h = hash_key(key) & m.mask;
     for (;;)
@@ -144,28 +148,15 @@ __device__ __forceinline__ u32 find_or_insert_cnt(const VoxelMapDev& m, u64 key,
         if (k == key && v.z != VID_INVALID)
         {
             cntword = v.w == 0xFFFFFFFFu ? 0u : v.w;
-            return v.z;
+            vid     = v.z;
+            return PROBE_FOUND;
         }
         if (k == KEY_EMPTY)
         {
             k = atomicCAS(reinterpret_cast<u64*>(&e->key), KEY_EMPTY, key);
-            if (k == KEY_EMPTY)
-            {
-                const u32 vid = alloc_row(m);
-                e->cnt        = 0;
-                __threadfence();
-                atomicExch(&e->vid, vid);
-                cntword = 0;
-                return vid;
-            }
+            if (k == KEY_EMPTY) return PROBE_CLAIMED;
         }
-        if (k == key)
-        {   // being created by another thread of this batch
-            u32 r;
-            while ((r = *reinterpret_cast<volatile u32*>(&e->vid)) == VID_INVALID) {}
-            cntword = 0;
-            return r;
-        }
+        if (k == key) return PROBE_PENDING;
         h = (h + 1) & m.mask;
     }
 }
@@ -205,7 +196,30 @@ __global__ void __launch_bounds__(RANK_BLOCK)
     const u32 peers  = __match_any_sync(MMG_FULL, key);
     const int leader = __ffs(peers) - 1;
     u32       vid = VID_INVALID, cw = 0, ent = 0;
-    if (ok && lane == leader) vid = find_or_insert_cnt(m, key, cw, ent);
+    int       st  = PROBE_NONE;
+    if (ok && lane == leader) st = probe_or_claim(m, key, vid, cw, ent);
+    {   // new voxels of this warp: one update of the row counter for all of them (the free-row stack only holds
+        // something after evictions; its slow path then takes rows one by one), then publish; the counters' cache line
+        // sees one atomic per warp instead of three per voxel
+        const u32 claimed = __ballot_sync(MMG_FULL, st == PROBE_CLAIMED);
+        if (claimed)
+        {
+            const bool stack_empty = *reinterpret_cast<volatile u32*>(&m.ctr->free_n) == 0u;
+            u32        row0        = 0;
+            if (stack_empty && lane == __ffs(claimed) - 1) row0 = atomicAdd(&m.ctr->nvox_hi, (u32)__popc(claimed));
+            row0 = __shfl_sync(MMG_FULL, row0, __ffs(claimed) - 1);
+            if (st == PROBE_CLAIMED)
+            {
+                vid      = stack_empty ? row0 + (u32)__popc(claimed & ((1u << lane) - 1u)) : alloc_row(m);
+                Entry* e = m.table + ent;
+                e->cnt   = 0;
+                __threadfence();
+                atomicExch(&e->vid, vid);
+            }
+        }
+        if (st == PROBE_PENDING)
+            while ((vid = *reinterpret_cast<volatile u32*>(&m.table[ent].vid)) == VID_INVALID) {}
+    }
     vid = __shfl_sync(MMG_FULL, vid, leader);
     cw  = __shfl_sync(MMG_FULL, cw, leader);
     ent = __shfl_sync(MMG_FULL, ent, leader);
@@ -224,6 +238,7 @@ __global__ void __launch_bounds__(RANK_BLOCK)
         u32       pos   = 0;
         if (want && lane == first) pos = atomicAdd(m.fill + vid, (u32)__popc(want));
         pos = __shfl_sync(MMG_FULL, pos, first < 0 ? lane : first);
+        bool lists = false;
         if (want >> lane & 1u)
         {
             const u32 s = pos + (u32)__popc(want & ((1u << lane) - 1u));
@@ -231,10 +246,18 @@ __global__ void __launch_bounds__(RANK_BLOCK)
             {
                 *reinterpret_cast<volatile u32*>(slot_w(m.pts + (size_t)vid * CAP + n0 + s)) = x;
                 alive = false;
-                if (s == 0) touched[atomicAdd(&m.ctr->nseg, 1u) - seg_base] = vid;  // lists the voxel for k_insert_commit
+                lists = s == 0;  // the point that gets the first free slot lists the voxel for k_insert_commit
             }
             // the group that takes the last free slot tells later probes to skip the counter
             if (lane == first && pos < room && pos + (u32)__popc(want) >= room) atomicMax(&m.table[ent].cnt, (1u << RANK_CNT_BITS) | n0);
+        }
+        const u32 lm = __ballot_sync(MMG_FULL, lists);
+        if (lm)
+        {   // one list-cursor update per warp
+            u32 at = 0;
+            if (lane == __ffs(lm) - 1) at = atomicAdd(&m.ctr->nseg, (u32)__popc(lm));
+            at = __shfl_sync(MMG_FULL, at, __ffs(lm) - 1);
+            if (lists) touched[at + (u32)__popc(lm & ((1u << lane) - 1u)) - seg_base] = vid;
         }
     }
     // Replacement phase: only for points that found every free slot handed out (voxels hit by several warps at once:
