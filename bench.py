@@ -58,18 +58,22 @@ def map_scans(target_points, count_fn, insert_fn, log=None):
     return k, n_in
 
 
-def query_batch(n_scans_in_map, rank=0, n=N_QUERIES):
-    """n query points in the map frame: consecutive scans taken mid-trajectory, each re-posed by a
-    small SE(3) step (one ICP iteration's pose guess), truncated to n. Every rank takes its own stretch of road, 50 m
-    apart. (Dealing one run of scans round-robin to the ranks instead spreads each rank's queries over 8 x the map area:
-    more rows come from DRAM after the L2 flush, 0.187-0.199 ms per step on all 8 ranks against 0.172-0.193.)"""
+def query_batch(n_scans_in_map, rank=0, n=N_QUERIES, world=1):
+    """n query points in the map frame: consecutive scans taken mid-trajectory, each re-posed by a small SE(3) step (one
+    ICP iteration's pose guess), truncated to n. Several ranks shard "scan points x ICP iterations": every rank holds the
+    same scans under its own pose guess (a 0.10 m step in its own direction, +-0.5 deg of yaw; rank 0 = the N = 1 batch),
+    so all ranks work on the same stretch of road. (A stretch of road per rank, 50 m apart, made the slowest stretch set
+    the step, 0.172-0.193 ms at N = 8; dealing one run of scans round-robin spread each rank's queries over 8 x the map
+    area, 0.187-0.199 ms: profiles/r1i_bench_n8.json, r1j_bench_n8_round_robin_queries.json.)"""
     from mola_b200 import synth
     out = [[], [], []]
     have, j = 0, 0
-    s0 = SPACING * (n_scans_in_map // 2) + 1.7 + 50.0 * rank
+    s0 = SPACING * (n_scans_in_map // 2) + 1.7
+    phi = 2.0 * np.pi * rank / max(world, 1)
     while have < n:
-        xs, ys, zs, pose = synth.lidar_scan("hdl64", s=s0 + 1.0 * j, seed=2, scan_id=100000 + 1000 * rank + j)
-        g = compose_host(synth.perturbed_pose(pose), xs, ys, zs)
+        xs, ys, zs, pose = synth.lidar_scan("hdl64", s=s0 + 1.0 * j, seed=2, scan_id=100000 + j)
+        guess = synth.perturbed_pose(pose, dx=0.10 * np.cos(phi), dy=0.10 * np.sin(phi), dyaw_deg=0.5 if rank % 2 == 0 else -0.5)
+        g = compose_host(guess, xs, ys, zs)
         for a in range(3):
             out[a].append(g[a])
         have += xs.size
@@ -335,7 +339,7 @@ def run_gpu(args, rank, world, local_rank):
     scan_insert = bench_scan_insert(gmap, nscans, dev, stream) if rank == 0 else None
 
     # ---- queries ---------------------------------------------------------------------------
-    q = query_batch(nscans, rank)
+    q = query_batch(nscans, rank, world=world)
     n = q[0].size
     hq = [torch.from_numpy(a).pin_memory() for a in q]                       # pinned host inputs
     dq = [a.to(dev, non_blocking=True) for a in hq]                          # HBM-resident inputs
@@ -438,7 +442,7 @@ def run_gpu(args, rank, world, local_rank):
             "config": {"workload": "C2: 10M-pt HashedVoxelPointCloud (voxel 0.5 m), batched nn_single_search of 1M points per step per GPU",
                        "map_points": int(stats["points"]), "map_voxels": int(stats["live_voxels"]), "map_scans": nscans,
                        "queries_per_step_per_gpu": n, "l2": "flushed between steps (256 MiB write)", "map_hbm_bytes": int(stats["hbm_bytes"]),
-                       "parallelism": f"map replicated by NCCL broadcast, queries sharded x{world}", "rank0_cpu_binding": numa},
+                       "parallelism": f"map replicated by NCCL broadcast, queries sharded x{world} (scan points x ICP pose guesses: one guess per rank)", "rank0_cpu_binding": numa},
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": 12 * n, "d2h_bytes_per_step": 25 * n},
             "gpu_launches": int(launches), "ms_per_step_by_rank": per_rank,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,

@@ -53,10 +53,10 @@ def lidar_scan(sensor="hdl64", s=0.0, seed=1, scan_id=0, noise=0.02, max_range=1
     return xs, ys, zs, pose
 
 
-def perturbed_pose(pose12, dx=0.10, dyaw_deg=0.5):
+def perturbed_pose(pose12, dx=0.10, dyaw_deg=0.5, dy=0.0):
     """pose12 composed with a small SE(3) step: mimics the pose guess of one ICP iteration."""
     R = pose12[:9].reshape(3, 3)
     t = pose12[9:]
     a = np.deg2rad(dyaw_deg)
     dR = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]])
-    return np.concatenate([(R @ dR).reshape(9), t + R @ np.array([dx, 0.0, 0.0])])
+    return np.concatenate([(R @ dR).reshape(9), t + R @ np.array([dx, dy, 0.0])])
