@@ -112,10 +112,20 @@ int mmg_get_params(const mmg_map* m, mmg_params* p);
 int mmg_reserve(mmg_map* m, uint64_t voxels);
 
 /* Inserts n points in input order (per-voxel decimation identical to calling the
- * reference's insertPoint once per point). has_robot_pose!=0 enables the
- * far-voxel eviction step with pose12's translation as the sensor position. */
+ * reference's insertPoint once per point). `flags` (historically "has_robot_pose"):
+ *   MMG_INSERT_ROBOT_POSE    pose12 is the robot pose of internal_insertObservation: run the far-voxel / far-block
+ *                            eviction first, with pose12's translation as the sensor position
+ *   MMG_INSERT_NO_CLEARANCE  SparseTrees only: append every point without the minimum_points_clearance test, i.e. the
+ *                            reference's public insertPoint() (SparseTreesPointCloud.h:224-234) called once per point,
+ *                            which is what its CObservation3DRangeScan::points3D branch does (SparseTreesPointCloud.cpp:349-356);
+ *                            ignored by the voxel maps, whose insertPoint() is the decimating one */
+enum
+{
+    MMG_INSERT_ROBOT_POSE   = 1,
+    MMG_INSERT_NO_CLEARANCE = 2
+};
 int mmg_insert_batch(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n,
-                     const double* pose12, int has_robot_pose, int mem, void* stream);
+                     const double* pose12, int flags, int mem, void* stream);
 
 /* Several scans in one call: scan s = points [scan_offsets[s], scan_offsets[s+1]) with pose
  * poses12 + 12*s (scan_offsets and poses12 are HOST arrays; the points follow `mem`).
@@ -200,6 +210,10 @@ int mmg_comm_unique_id(uint8_t out_id[128]);
 int mmg_comm_init(const uint8_t id[128], int rank, int nranks, int device, mmg_comm** out);
 int mmg_comm_destroy(mmg_comm* c);
 int mmg_bcast(mmg_map* m, mmg_comm* c, int root, void* stream);
+
+/* Diagnostics: process-wide A/B switches for the profiles ("nn_kernel", "nn_gw", "nn_minb", "nn_permute"); results are
+ * identical for every setting, only the kernel organisation changes. */
+int mmg_set_tuning(const char* key, int value);
 
 /* Number of kernels this library has launched in the calling process. */
 uint64_t    mmg_kernel_launch_count(void);

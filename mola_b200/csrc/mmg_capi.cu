@@ -18,7 +18,8 @@
 
 namespace mmg
 {
-unsigned long long        g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
+int                       g_tune[T_COUNT] = {0, 8, 4096, 1};
 static thread_local char  g_err[512] = "";
 void set_error(const char* fmt, ...)
 {
@@ -39,8 +40,68 @@ PoseD mmg::make_pose(const double* pose12)
     return T;
 }
 
+namespace mmg
+{
+static thread_local ScratchScope* t_scope = nullptr;
+// per-thread hit buffers of the radius searches (S_RHITS, S_RHITS2): grow-only, released when the thread ends
+struct TlsRad
+{
+    void*     buf[2] = {nullptr, nullptr};
+    size_t    cap[2] = {0, 0};
+    RadResult r;
+    ~TlsRad()
+    {
+        for (void* b : buf)
+            if (b) cudaFree(b);
+        cudaGetLastError();
+    }
+    void* get(int i, size_t bytes)
+    {
+        if (cap[i] < bytes)
+        {
+            if (buf[i]) cudaFree(buf[i]);  // synchronises the device: the previous hits are no longer in use
+            buf[i] = nullptr, cap[i] = 0;
+            const size_t want = bytes + bytes / 4 + 256;
+            if (cudaMalloc(&buf[i], want) != cudaSuccess)
+            {
+                set_error("cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(cudaGetLastError()));
+                return nullptr;
+            }
+            cap[i] = want;
+        }
+        return buf[i];
+    }
+};
+static thread_local TlsRad t_rad;
+RadResult&                 rad_result() { return t_rad.r; }
+
+ScratchScope::ScratchScope(cudaStream_t st) : st_(st), prev_(t_scope) { t_scope = this; }
+ScratchScope::~ScratchScope()
+{
+    for (void* p : all_) cudaFreeAsync(p, st_);
+    t_scope = prev_;
+}
+void* ScratchScope::get(int slot, size_t bytes)
+{
+    if (slot == S_RHITS || slot == S_RHITS2) return t_rad.get(slot == S_RHITS ? 0 : 1, bytes);
+    if (slot >= (int)slots_.size()) slots_.resize(slot + 1, {nullptr, 0});
+    auto& s = slots_[slot];
+    if (s.second >= bytes && s.first) return s.first;
+    void* p = nullptr;  // an outgrown block stays alive until the scope ends: kernels already enqueued may still use it
+    if (cudaMallocAsync(&p, bytes + 256, st_) != cudaSuccess)
+    {
+        set_error("cudaMallocAsync(%zu) failed: %s", bytes + 256, cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    all_.push_back(p);
+    s = {p, bytes + 256};
+    return p;
+}
+}  // namespace mmg
+
 void* mmg_map::scratch_get(int slot, size_t bytes)
 {
+    if (mmg::t_scope) return mmg::t_scope->get(slot, bytes);
     if (slot >= (int)scratch.size()) scratch.resize(slot + 1, {nullptr, 0});
     auto& s = scratch[slot];
     if (s.second < bytes)
@@ -363,14 +424,45 @@ struct OutBufs
 };
 
 template <class Tr>
-static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy, const float* dz, size_t nq, size_t stride, const PoseD& T, int use_pose,
+static int launch_nn_single(const mmg_map* m, const float* dx, const float* dy, const float* dz, size_t nq, size_t stride, const PoseD& T, int use_pose,
                              const QueryOut& o, cudaStream_t st, float bd_init = INFINITY)
 {
-    // A/B switch for the profiles: MMG_NN_KERNEL = pruned (default) | grouped | simple
-    static const int variant = [] {
+    // A/B switch for the profiles: MMG_NN_KERNEL = tasks (default) | pruned | grouped | simple, or mmg_set_tuning("nn_kernel", 0..3)
+    static const int env_variant = [] {
         const char* e = getenv("MMG_NN_KERNEL");
-        return !e ? 0 : (!strcmp(e, "grouped") ? 1 : (!strcmp(e, "simple") ? 2 : 0));
+        return !e ? -1 : (!strcmp(e, "pruned") ? 1 : (!strcmp(e, "grouped") ? 2 : (!strcmp(e, "simple") ? 3 : 0)));
     }();
+    const int kv = env_variant >= 0 ? env_variant : g_tune[T_NN_KERNEL];
+    if (kv == 0 && nq >= (size_t)g_tune[T_NN_MIN_PIPE])
+    {   // three-kernel pipeline over a global task queue (mmg_query.cuh); its scratch comes from the stream-ordered pool, so
+        // concurrent callers on one map never share state
+        const size_t c0 = std::min<size_t>(nq, NN_CHUNK);
+        const size_t off_key = 16 * c0, off_q = off_key + 8 * c0, off_cnt = off_q + 104 * c0;
+        char*        wb = nullptr;
+        if (cudaMallocAsync((void**)&wb, off_cnt + 16, st) != cudaSuccess)
+        {
+            cudaGetLastError();
+            set_error("cudaMallocAsync(%zu) failed", off_cnt + 16);
+            return MMG_ERR_OUT_OF_MEM;
+        }
+        NNWork W;
+        W.qpt = (float4*)wb, W.qkey = (u64*)(wb + off_key), W.count = (u32*)(wb + off_cnt);
+        W.queue[0] = (u32*)(wb + off_q), W.queue[1] = W.queue[0] + 6 * c0, W.queue[2] = W.queue[1] + 12 * c0;
+        for (size_t a = 0; a < nq; a += NN_CHUNK)
+        {
+            const u32 k = (u32)std::min<size_t>(NN_CHUNK, nq - a);
+            cudaMemsetAsync(W.count, 0, 16, st);
+            QueryOut oc{o.found + a, o.xyz + 3 * a, o.d2 + a, o.id + a};
+            MMG_LAUNCH((k_nn_own<Tr>), (k + NN_OWN_BLOCK - 1) / NN_OWN_BLOCK, NN_OWN_BLOCK, 0, st, m->dev, dx + a * stride, dy + a * stride, dz + a * stride, k,
+                       (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, bd_init, W);
+            const unsigned tb = (unsigned)std::min<size_t>(((size_t)k * 26 + 255) / 256, (size_t)m->num_sms * g_tune[T_NN_TASK_BLOCKS]);
+            MMG_LAUNCH((k_nn_tasks<Tr>), tb, 256, 0, st, m->dev, m->inv, m->prm.voxel_size, W);
+            MMG_LAUNCH((k_nn_finish<Tr>), (k + 255) / 256, 256, 0, st, m->dev, k, m->inv, W, oc);
+        }
+        cudaFreeAsync(wb, st);
+        return MMG_OK;
+    }
+    const int variant = kv - 1;
     if (variant == 2 && bd_init == INFINITY)
     {
         const unsigned nb = persistent_blocks(m, nq, 8, 8);
@@ -415,6 +507,7 @@ static void launch_nn_single(const mmg_map* m, const float* dx, const float* dy,
             default: MMG_LAUNCH((k_nn_single_pruned<Tr, 5, false>), nb, bs, 0, st, m->dev, dx, dy, dz, (u32)nq, (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, o, bd_init, perm); break;
         }
     }
+    return MMG_OK;
 }
 
 template <class Tr>
@@ -427,9 +520,9 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
     const PoseD  T  = make_pose(pose12);
     if (mem == MMG_MEM_DEVICE)
     {
-        launch_nn_single<Tr>(m, xs, ys, zs, nq, stride, T, pose12 ? 1 : 0, QueryOut{ofound, oxyz, od2, (u64*)oid}, st, bd_init);
+        const int rc = launch_nn_single<Tr>(m, xs, ys, zs, nq, stride, T, pose12 ? 1 : 0, QueryOut{ofound, oxyz, od2, (u64*)oid}, st, bd_init);
         MMG_CUDA(cudaGetLastError());
-        return MMG_OK;
+        return rc;
     }
     // Pinned (page-locked, mapped) host buffers: ONE launch reads the queries and writes the results straight over PCIe
     // (coalesced loads / whole-line stores, both directions busy at once, no staging copies, no per-chunk copy calls).
@@ -448,8 +541,9 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
         cudaGetLastError();
         if (all)
         {
-            launch_nn_single<Tr>(m, (const float*)dp[0], (const float*)dp[1], (const float*)dp[2], nq, 1, T, pose12 ? 1 : 0,
-                                 QueryOut{(uint8_t*)dp[3], (float*)dp[4], (float*)dp[5], (u64*)dp[6]}, st, bd_init);
+            const int rc = launch_nn_single<Tr>(m, (const float*)dp[0], (const float*)dp[1], (const float*)dp[2], nq, 1, T, pose12 ? 1 : 0,
+                                                QueryOut{(uint8_t*)dp[3], (float*)dp[4], (float*)dp[5], (u64*)dp[6]}, st, bd_init);
+            if (rc) return rc;
             MMG_CUDA(cudaGetLastError());
             MMG_CUDA(cudaStreamSynchronize(st));
             return MMG_OK;
@@ -463,6 +557,7 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
         set_error("strided queries take device buffers");
         return MMG_ERR_INVALID_ARG;
     }
+    std::lock_guard<std::mutex> pipe_lock(m->pipe_mtx);
     int rc = m->ensure_pipeline();
     if (rc) return rc;
     float* b  = (float*)m->scratch_get(S_IN, 3 * n * sizeof(float));
@@ -487,7 +582,7 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
         MMG_CUDA(cudaMemcpyAsync(b + 2 * n + a, zs + a, k * sizeof(float), cudaMemcpyHostToDevice, m->s_in));
         MMG_CUDA(cudaEventRecord(m->ev_in[c], m->s_in));
         MMG_CUDA(cudaStreamWaitEvent(st, m->ev_in[c], 0));
-        launch_nn_single<Tr>(m, b + a, b + n + a, b + 2 * n + a, k, 1, T, pose12 ? 1 : 0, QueryOut{dfn + a, dxyz + 3 * a, dd2 + a, did + a}, st);
+        if ((rc = launch_nn_single<Tr>(m, b + a, b + n + a, b + 2 * n + a, k, 1, T, pose12 ? 1 : 0, QueryOut{dfn + a, dxyz + 3 * a, dd2 + a, did + a}, st))) return rc;
         MMG_CUDA(cudaEventRecord(m->ev_k[c], st));
         MMG_CUDA(cudaStreamWaitEvent(m->s_out, m->ev_k[c], 0));
         MMG_CUDA(cudaMemcpyAsync(oxyz + 3 * a, dxyz + 3 * a, k * 12, cudaMemcpyDeviceToHost, m->s_out));
@@ -554,13 +649,13 @@ static int radius_hashed(mmg_map* m, const float* xs, const float* ys, const flo
     u64 total = 0;
     MMG_CUDA(cudaMemcpyAsync(&total, offs + n, sizeof(u64), cudaMemcpyDeviceToHost, st));
     MMG_CUDA(cudaStreamSynchronize(st));
-    m->rad_total = total;
+    rad_result().total = total;
     char* hb     = (char*)m->scratch_get(S_RHITS, std::max<u64>(total, 1) * 24);
     if (!hb) return MMG_ERR_OUT_OF_MEM;
-    m->rad_id = (u64*)hb, m->rad_xyz = (float*)(hb + total * 8), m->rad_d2 = (float*)(hb + total * 20);
+    rad_result().id = (u64*)hb, rad_result().xyz = (float*)(hb + total * 8), rad_result().d2 = (float*)(hb + total * 20);
     if (total)
-        MMG_LAUNCH((k_radius_hashed<Tr, 1>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, m->prm.voxel_size, r2, r, mp, counts, offs, m->rad_xyz,
-                   m->rad_d2, m->rad_id);
+        MMG_LAUNCH((k_radius_hashed<Tr, 1>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, m->prm.voxel_size, r2, r, mp, counts, offs, rad_result().xyz,
+                   rad_result().d2, rad_result().id);
     MMG_CUDA(cudaGetLastError());
     if (mem == MMG_MEM_HOST)
         MMG_CUDA(cudaMemcpyAsync(ooff, offs, (n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, st));
@@ -604,6 +699,7 @@ extern "C" int mmg_match_batch(const mmg_map* cm, const float* xs, const float* 
                                int mem, void* stream)
 {
     MMG_CHECK_MAP(cm);
+    ScratchScope scratch_scope((cudaStream_t)stream);
     mmg_map* m = const_cast<mmg_map*>(cm);
     if (!out_count || (n && (!xs || !ys || !zs || !out_local_idx || !out_xyz || !out_d2 || !out_id)) || n >= (1ull << 31)) return MMG_ERR_INVALID_ARG;
     *out_count = 0;
@@ -708,6 +804,13 @@ int mmg_create(int kind, const mmg_params* p, int device, mmg_map** out)
     MMG_CUDA(cudaDeviceGetAttribute(&m->num_sms, cudaDevAttrMultiProcessorCount, device));
     MMG_CUDA(cudaMalloc(&m->dev.ctr, sizeof(Counters)));
     MMG_CUDA(cudaMallocHost(&m->h_ctr, sizeof(Counters)));
+    {   // the query pipelines take their scratch from the stream-ordered pool: keep freed blocks cached instead of
+        // returning them to the driver at every synchronisation
+        cudaMemPool_t pool;
+        uint64_t      keep = UINT64_MAX;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        cudaGetLastError();
+    }
     int rc = init_counters(m, false);
     if (!rc && kind != MMG_SPARSE_TREES) rc = alloc_table(m, 1u << 16);
     if (!rc && kind == MMG_SPARSE_TREES) rc = trees_create(m);
@@ -794,8 +897,8 @@ int mmg_insert_batch(mmg_map* m, const float* xs, const float* ys, const float* 
     cudaStream_t st = (cudaStream_t)stream;
     switch (m->kind)
     {
-        case MMG_HASHED_VOXEL: return insert_voxel<HashedTraits>(m, xs, ys, zs, n, pose12, has_robot_pose, mem, st);
-        case MMG_SPARSE_VOXEL: return insert_voxel<SparseVoxelTraits>(m, xs, ys, zs, n, pose12, has_robot_pose, mem, st);
+        case MMG_HASHED_VOXEL: return insert_voxel<HashedTraits>(m, xs, ys, zs, n, pose12, has_robot_pose & MMG_INSERT_ROBOT_POSE, mem, st);
+        case MMG_SPARSE_VOXEL: return insert_voxel<SparseVoxelTraits>(m, xs, ys, zs, n, pose12, has_robot_pose & MMG_INSERT_ROBOT_POSE, mem, st);
         default: return trees_insert(m, xs, ys, zs, n, pose12, has_robot_pose, mem, st);
     }
 }
@@ -818,7 +921,7 @@ int mmg_insert_scans(mmg_map* m, const float* xs, const float* ys, const float* 
     const mmg_params& P  = m->prm;
     // One fused pass is only equivalent to scan-by-scan insertion when nothing happens between the scans
     // (no eviction) and the per-voxel rule is the cap-only one; otherwise insert scan by scan.
-    const bool evicts = has_robot_pose && P.remove_voxels_farther_than > 0 && m->kind != MMG_SPARSE_VOXEL;
+    const bool evicts = (has_robot_pose & MMG_INSERT_ROBOT_POSE) && P.remove_voxels_farther_than > 0 && m->kind != MMG_SPARSE_VOXEL;
     const bool fused  = m->kind != MMG_SPARSE_TREES && !evicts && !(m->kind == MMG_HASHED_VOXEL && P.min_distance_between_points > 0.f) &&
                        n < (1ull << 31) && scan_offsets[0] == 0;
     if (!fused)
@@ -871,6 +974,7 @@ int mmg_nn_single_batch(const mmg_map* m, const float* xs, const float* ys, cons
                         float* out_xyz, float* out_d2, uint64_t* out_id, int mem, void* stream)
 {
     MMG_CHECK_MAP(m);
+    ScratchScope scratch_scope((cudaStream_t)stream);
     if (n && (!xs || !ys || !zs || !out_found || !out_xyz || !out_d2 || !out_id)) return MMG_ERR_INVALID_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     switch (m->kind)
@@ -888,6 +992,7 @@ int mmg_nn_multi_batch(const mmg_map* m, const float* xs, const float* ys, const
                        uint32_t* out_count, float* out_xyz, float* out_d2, uint64_t* out_id, int mem, void* stream)
 {
     MMG_CHECK_MAP(m);
+    ScratchScope scratch_scope((cudaStream_t)stream);
     if (k == 0)
     {  // ASSERT_(N > 0), HashedVoxelPointCloud.cpp:702
         set_error("nn_multiple_search: N must be > 0");
@@ -913,9 +1018,12 @@ int mmg_nn_radius_batch(mmg_map* m, const float* xs, const float* ys, const floa
                         size_t max_points, uint64_t* out_offsets, uint64_t* out_total, int mem, void* stream)
 {
     MMG_CHECK_MAP(m);
+    ScratchScope scratch_scope((cudaStream_t)stream);
     if (!out_offsets || (n && (!xs || !ys || !zs))) return MMG_ERR_INVALID_ARG;
     if (n >= (1ull << 31)) return MMG_ERR_INVALID_ARG;
     cudaStream_t st = (cudaStream_t)stream;
+    rad_result()    = RadResult{};
+    rad_result().owner = m;
     switch (m->kind)
     {
         case MMG_HASHED_VOXEL: return radius_hashed<HashedTraits>(m, xs, ys, zs, n, pose12, radius_sqr, max_points, out_offsets, out_total, mem, st);
@@ -928,12 +1036,18 @@ int mmg_nn_radius_fetch(mmg_map* m, float* out_xyz, float* out_d2, uint64_t* out
 {
     MMG_CHECK_MAP(m);
     cudaStream_t st = (cudaStream_t)stream;
-    const u64    t  = m->rad_total;
+    // the hits of the CALLING THREAD's last mmg_nn_radius_batch on this map
+    if (rad_result().owner != m)
+    {
+        set_error("mmg_nn_radius_fetch: this thread has no pending radius result for this map");
+        return MMG_ERR_INVALID_ARG;
+    }
+    const u64    t  = rad_result().total;
     if (!t) return MMG_OK;
     const cudaMemcpyKind k = mem == MMG_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
-    MMG_CUDA(cudaMemcpyAsync(out_xyz, m->rad_xyz, t * 12, k, st));
-    MMG_CUDA(cudaMemcpyAsync(out_d2, m->rad_d2, t * 4, k, st));
-    MMG_CUDA(cudaMemcpyAsync(out_id, m->rad_id, t * 8, k, st));
+    MMG_CUDA(cudaMemcpyAsync(out_xyz, rad_result().xyz, t * 12, k, st));
+    MMG_CUDA(cudaMemcpyAsync(out_d2, rad_result().d2, t * 4, k, st));
+    MMG_CUDA(cudaMemcpyAsync(out_id, rad_result().id, t * 8, k, st));
     if (mem == MMG_MEM_HOST) MMG_CUDA(cudaStreamSynchronize(st));
     return MMG_OK;
 }
@@ -942,6 +1056,7 @@ int mmg_likelihood(const mmg_map* cm, const float* xs, const float* ys, const fl
                    void* stream)
 {
     MMG_CHECK_MAP(cm);
+    ScratchScope scratch_scope((cudaStream_t)stream);
     mmg_map* m = const_cast<mmg_map*>(cm);
     if (!out_loglik) return MMG_ERR_INVALID_ARG;
     int empty = 0;
@@ -1104,6 +1219,7 @@ static int export_voxel(const mmg_map* cm, int32_t* keys, uint32_t* counts, floa
 int mmg_num_points(const mmg_map* m, uint64_t* out_n)
 {
     MMG_CHECK_MAP(m);
+    ScratchScope scratch_scope(nullptr);
     if (!out_n) return MMG_ERR_INVALID_ARG;
     if (m->kind == MMG_SPARSE_TREES) return trees_num_points(m, out_n);
     const u64 V = m->h_nvox_hi - m->h_free_n;
@@ -1121,6 +1237,7 @@ int mmg_num_points(const mmg_map* m, uint64_t* out_n)
 int mmg_export(const mmg_map* m, int32_t* out_keys, uint32_t* out_counts, float* out_points, int mem, void* stream)
 {
     MMG_CHECK_MAP(m);
+    ScratchScope scratch_scope((cudaStream_t)stream);
     if (m->kind == MMG_SPARSE_TREES) return trees_export(m, out_keys, out_counts, out_points, mem, (cudaStream_t)stream);
     return export_voxel(m, out_keys, out_counts, out_points, nullptr, nullptr, mem, (cudaStream_t)stream);
 }
@@ -1128,6 +1245,7 @@ int mmg_export(const mmg_map* m, int32_t* out_keys, uint32_t* out_counts, float*
 int mmg_voxel_stats(const mmg_map* m, float* out_mean, float* out_cov, int mem, void* stream)
 {
     MMG_CHECK_MAP(m);
+    ScratchScope scratch_scope((cudaStream_t)stream);
     if (m->kind != MMG_SPARSE_VOXEL)
     {
         set_error("voxel mean/covariance exist for SparseVoxelPointCloud only");
@@ -1156,6 +1274,7 @@ __global__ void k_probe_stats(VoxelMapDev m, u32 nrows, unsigned long long* sum,
 int mmg_get_table_stats(const mmg_map* cm, mmg_table_stats* out)
 {
     MMG_CHECK_MAP(cm);
+    ScratchScope scratch_scope(nullptr);
     mmg_map* m = const_cast<mmg_map*>(cm);
     if (!out) return MMG_ERR_INVALID_ARG;
     memset(out, 0, sizeof(*out));
@@ -1247,6 +1366,7 @@ __global__ void k_stencil_points(VoxelMapDev m, const float* __restrict__ qx, co
 int mmg_mean_stencil_points(const mmg_map* cm, const float* xs, const float* ys, const float* zs, size_t n, int mem, void* stream, double* out)
 {
     MMG_CHECK_MAP(cm);
+    ScratchScope scratch_scope((cudaStream_t)stream);
     mmg_map* m = const_cast<mmg_map*>(cm);
     if (!out || m->kind == MMG_SPARSE_TREES) return MMG_ERR_INVALID_ARG;
     *out = 0;
@@ -1264,6 +1384,19 @@ int mmg_mean_stencil_points(const mmg_map* cm, const float* xs, const float* ys,
     MMG_CUDA(cudaStreamSynchronize(st));
     *out = (double)h / (double)n;
     return MMG_OK;
+}
+
+int mmg_set_tuning(const char* key, int value)
+{
+    static const char* names[T_COUNT] = {"nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute"};
+    for (int i = 0; key && i < T_COUNT; i++)
+        if (!strcmp(key, names[i]))
+        {
+            g_tune[i] = value;
+            return MMG_OK;
+        }
+    set_error("mmg_set_tuning: unknown knob");
+    return MMG_ERR_INVALID_ARG;
 }
 
 uint64_t    mmg_kernel_launch_count(void) { return g_launches; }

@@ -102,7 +102,7 @@ inline int hits_map_semantics(mmg_map* m, u32 nq, u32 H, const u32* qkey, const 
     float* od2  = (float*)(hb + tot * 20);
     if (tot) MMG_LAUNCH(k_hits_compact, g, 256, 0, st, sk, p2, keep, ks, qstart, doff, H, maxp, sxyz, sd2, sid, oxyz, od2, oid);
     MMG_CUDA(cudaGetLastError());
-    m->rad_total = tot, m->rad_id = oid, m->rad_xyz = oxyz, m->rad_d2 = od2;
+    rad_result().total = tot, rad_result().id = oid, rad_result().xyz = oxyz, rad_result().d2 = od2;
     *total = tot;
     return MMG_OK;
 }

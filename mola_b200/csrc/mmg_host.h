@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
+#include <mutex>
 #include <utility>
 #include <vector>
 
@@ -48,6 +50,35 @@ enum ScratchSlot
     S_COUNT
 };
 struct TreesState;
+
+// Scratch of one const query call. While a scope is alive on the calling thread, mmg_map::scratch_get() hands out
+// blocks of the stream-ordered pool (cudaMallocAsync on the call's stream) that the scope returns when the call ends,
+// instead of the map's own grow-only slots: concurrent queries on one map (several host threads, several streams)
+// never share or re-allocate scratch. The hit buffers of a radius search outlive the call (mmg_nn_radius_fetch reads
+// them), so they belong to the calling thread instead (RadResult).
+struct ScratchScope
+{
+    explicit ScratchScope(cudaStream_t st);
+    ~ScratchScope();
+    ScratchScope(const ScratchScope&)            = delete;
+    ScratchScope& operator=(const ScratchScope&) = delete;
+    void*         get(int slot, size_t bytes);
+
+   private:
+    cudaStream_t                          st_;
+    ScratchScope*                         prev_;
+    std::vector<std::pair<void*, size_t>> slots_;
+    std::vector<void*>                    all_;
+};
+// Result of the calling thread's last mmg_nn_radius_batch (read by its next mmg_nn_radius_fetch).
+struct RadResult
+{
+    const mmg_map* owner = nullptr;
+    u64            total = 0;
+    u64*           id    = nullptr;
+    float *        xyz = nullptr, *d2 = nullptr;
+};
+RadResult& rad_result();
 }  // namespace mmg
 
 struct mmg_map
@@ -63,16 +94,13 @@ struct mmg_map
     void*            h_stage = nullptr;  // pinned staging block (scan poses + offsets of mmg_insert_scans)
     size_t           h_stage_bytes = 0;
     bool             points_dirty = false;
-    // radius results of the last mmg_nn_radius_batch
-    mmg::u64  rad_total = 0;
-    mmg::u64* rad_id    = nullptr;
-    float *   rad_xyz = nullptr, *rad_d2 = nullptr;
     // SparseTrees
     mmg::TreesState* trees = nullptr;
     // host-buffer pipeline (H2D | kernel | D2H overlapped in chunks), created on first use
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t  ev_start = nullptr, ev_in[8] = {}, ev_k[8] = {};
     int          ensure_pipeline();
+    std::mutex   pipe_mtx;  // the pageable-host-buffer pipeline (streams + events above) serves one call at a time
     // grow-only device scratch
     std::vector<std::pair<void*, size_t>> scratch;
     void*                                 scratch_get(int slot, size_t bytes);
@@ -105,6 +133,16 @@ int trees_table_stats(mmg_map* m, mmg_table_stats* out);
 
 namespace mmg
 {
+// runtime tuning knobs (mmg_set_tuning): A/B switches for the profiles, defaults = the measured best
+enum Tune
+{
+    T_NN_KERNEL = 0,    // 0 = task-queue pipeline (k_nn_own/_tasks/_finish), 1 = k_nn_single_pruned, 2 = grouped, 3 = simple
+    T_NN_TASK_BLOCKS,   // blocks of 256 per SM of k_nn_tasks
+    T_NN_MIN_PIPE,      // batches smaller than this take the single-kernel path (one launch, no scratch)
+    T_NN_PERMUTE,       // k_nn_single_pruned: scattered tile order on/off
+    T_COUNT
+};
+extern int g_tune[T_COUNT];
 int      alloc_table(mmg_map* m, u64 cap);
 int      ensure_rows(mmg_map* m, u64 rows, cudaStream_t st);
 int      read_counters(mmg_map* m, Counters* c, cudaStream_t st);

@@ -338,3 +338,210 @@ __global__ void __launch_bounds__(256, MINB)
     }
 }
 }  // namespace mmg
+
+namespace mmg
+{
+// ---------------------------------------------------------------------------------------------
+// nn_single_search as a three-kernel pipeline over a global task queue (the default since round 2).
+//
+// k_nn_single_pruned (above) does the whole branch-and-bound in one thread per query. Its two measured losses (ncu,
+// round 1: 17 of 32 lanes active, SMs busy 74 % of the launch) both come from the neighbour visits: a few lanes of a
+// warp have many cells left while the others idle, and runs of such queries form the kernel's tail. Pooling the visits
+// per warp (tried first, round 2a) balances lanes but serialises a heavy tile's visits into hundreds of dependent
+// rounds. So the visits leave the warp altogether:
+//   k_nn_own    one thread per query: compose, voxel index, the query's OWN voxel (sets the bound; lanes of a warp
+//               mostly share the row, so the loads are broadcasts). Stores the composed point and the packed result
+//               key {d2 bits : cell*32+slot} per query and appends one 4-byte task {cell : query} for every neighbour
+//               cell whose box can still hold a point at least as close, to the face / edge / corner queue. One
+//               atomicAdd per block and queue; inside a warp the tasks are laid out cell-major, so consecutive tasks
+//               are consecutive scan points looking at the same neighbour cell: the same row more often than not.
+//   k_nn_tasks  one thread per task, all queues in tier order: re-check the cell's lower bound against the query's
+//               CURRENT key (tightened by every task that finished before), probe, walk the row, 64-bit atomicMin.
+//               Every task is at most one 32-point row, so a plain grid-stride loop is balanced by construction and
+//               every lane has work.
+//   k_nn_finish one thread per query: unpack the key, fetch the winning point, write the four outputs coalesced.
+// The key order (d2, cell*32+slot) is exactly the reference's "first candidate in scan order wins ties" (strict '<'
+// at HashedVoxelPointCloud.cpp:728); pruning only drops cells whose every point is strictly farther than the bound,
+// so the result is the exhaustive walk's, bit for bit, whatever order the tasks run in.
+struct NNWork
+{
+    float4* qpt;       // composed query points (w unused)
+    u64*    qkey;      // per query {d2 bits : rank}; rank 0xFFFFFFFF = nothing found yet
+    u32*    queue[3];  // face / edge / corner tasks: cell (5 bits) << 27 | query (27 bits)
+    u32*    count;     // [3] queue tails
+};
+constexpr u32 NN_FACE = 0x415410u, NN_EDGE = 0x2aa8aaau, NN_CORNER = 0x7FFFFFFu & ~(NN_FACE | NN_EDGE | (1u << 13));
+constexpr u32 NN_CHUNK = 1u << 20;  // queries per pipeline pass (task ids hold 27 bits; bounds the worst-case queue size)
+constexpr int NN_OWN_BLOCK = 256;
+
+template <class Tr>
+__global__ void __launch_bounds__(NN_OWN_BLOCK)
+    k_nn_own(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride, PoseD pose,
+             int use_pose, float inv, float vsize, float bd_init, NNWork w)
+{
+    constexpr int NW = NN_OWN_BLOCK / 32;
+    __shared__ u32 s_cnt[3][NW];
+    __shared__ u32 s_base[3];
+    const int  lane = lane_id(), wid = threadIdx.x >> 5;
+    const u32  q     = blockIdx.x * NN_OWN_BLOCK + threadIdx.x;
+    const bool valid = q < n;
+    float3     p     = make_float3(0.f, 0.f, 0.f);
+    int        cx = 0, cy = 0, cz = 0;
+    bool       ok = false;
+    if (valid)
+    {
+        const size_t qi = (size_t)q * stride;
+        p               = make_float3(qx[qi], qy[qi], qz[qi]);
+        if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
+        ok = Tr::to_index(p.x, inv, cx) & Tr::to_index(p.y, inv, cy) & Tr::to_index(p.z, inv, cz);
+    }
+    float bd = bd_init;
+    u32   br = 0xFFFFFFFFu, bv = 0, t = 0;
+    if (ok)
+    {
+        float gx[3], gy[3], gz[3];
+        nn_axis_gaps<Tr>(cx, vsize, p.x, gx);
+        nn_axis_gaps<Tr>(cy, vsize, p.y, gy);
+        nn_axis_gaps<Tr>(cz, vsize, p.z, gz);
+        nn_visit_cell<Tr, true>(m, 13, cx, cy, cz, p, bd, br, bv);
+#pragma unroll
+        for (int b = 0; b < 27; b++)
+            if (b != 13 && !(gx[b / 9] + gy[(b / 3) % 3] + gz[b % 3] > bd)) t |= 1u << b;
+    }
+    if (valid)
+    {
+        w.qpt[q]  = make_float4(p.x, p.y, p.z, 0.f);
+        w.qkey[q] = ((u64)__float_as_uint(bd) << 32) | (u64)br;
+    }
+    // queue space: per-warp counts -> one atomicAdd per block and queue
+    const u32 TIER[3] = {NN_FACE, NN_EDGE, NN_CORNER};
+    u32       wcnt[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {
+        wcnt[k] = __reduce_add_sync(MMG_FULL, (u32)__popc(t & TIER[k]));
+        if (lane == 0) s_cnt[k][wid] = wcnt[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 3)
+    {
+        u32 tot = 0;
+#pragma unroll
+        for (int i = 0; i < NW; i++) tot += s_cnt[threadIdx.x][i];
+        s_base[threadIdx.x] = tot ? atomicAdd(&w.count[threadIdx.x], tot) : 0u;
+    }
+    __syncthreads();
+    const u32 any = __reduce_or_sync(MMG_FULL, t);
+    if (!any) return;
+    const u32 lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {
+        if (!wcnt[k]) continue;
+        u32 o = s_base[k];
+        for (int i = 0; i < wid; i++) o += s_cnt[k][i];
+        u32* Q = w.queue[k];
+        for (u32 r = any & TIER[k]; r; r &= r - 1)
+        {   // cell-major inside the warp
+            const int b   = __ffs(r) - 1;
+            const u32 bal = __ballot_sync(MMG_FULL, (t >> b) & 1u);
+            if ((t >> b) & 1u) Q[o + __popc(bal & lt)] = ((u32)b << 27) | q;
+            o += __popc(bal);
+        }
+    }
+}
+
+template <class Tr>
+__global__ void __launch_bounds__(256)
+    k_nn_tasks(VoxelMapDev m, float inv, float vsize, NNWork w)
+{
+    constexpr int CAP     = Tr::CAP;
+    const u32     gtid    = blockIdx.x * blockDim.x + threadIdx.x, gstride = gridDim.x * blockDim.x;
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {   // unrolled: the queue pointers stay in registers (a dynamic index would put the parameter block on the stack)
+        const u32  cnt = w.count[k];
+        const u32* Q   = w.queue[k];
+#pragma unroll 1
+        for (u32 i = gtid; i < cnt; i += gstride)
+        {
+            const u32    tk = __ldg(Q + i);
+            const u32    q = tk & 0x7FFFFFFu;
+            const int    b = (int)(tk >> 27);
+            const float4 p = __ldg(w.qpt + q);
+            const u64    key0 = __ldcg(w.qkey + q);  // L2: sees what the tasks that finished so far have found
+            int          cx, cy, cz;
+            Tr::to_index(p.x, inv, cx), Tr::to_index(p.y, inv, cy), Tr::to_index(p.z, inv, cz);
+            const int x = cx + b / 9 - 1, y = cy + (b / 3) % 3 - 1, z = cz + b % 3 - 1;
+            if (!index_in_range(x, y, z)) continue;
+            const float bd = __uint_as_float((u32)(key0 >> 32));
+            if (voxel_lower_bound<Tr>(x, y, z, vsize, p.x, p.y, p.z) > bd) continue;
+            u32 vid, c;
+            if (!probe_ro(m.table, m.mask, pack_key(x, y, z), vid, c) || !c) continue;
+            const float4* row = m.pts + (size_t)vid * CAP;
+            if (c > 8) asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 8));
+            if (c > 16) asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 16));
+            if (c > 24) asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 24));
+            unsigned long long qxy;
+            asm("mov.b64 %0, {%1,%2};" : "=l"(qxy) : "f"(p.x), "f"(p.y));
+            float cd = __int_as_float(0x7f800000);
+            u32   cs = 0;
+#pragma unroll 4
+            for (u32 s = 0; s < c; s++)
+            {
+                const float d = sqr_dist_packed(__ldg(row + s), qxy, p.z);
+                if (d < cd) cd = d, cs = s;
+            }
+            const u64 key = ((u64)__float_as_uint(cd) << 32) | (u64)((u32)b * 32u + cs);
+            if (key < key0) atomicMin(w.qkey + q, key);
+        }
+    }
+}
+
+template <class Tr>
+__global__ void __launch_bounds__(256)
+    k_nn_finish(VoxelMapDev m, u32 n, float inv, NNWork w, QueryOut out)
+{
+    constexpr int CAP  = Tr::CAP;
+    const int     lane = lane_id();
+    const u32     q0   = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u;
+    const u32     q    = q0 + (u32)lane;
+    if (q0 >= n) return;
+    const bool valid = q < n;
+    float4     t     = make_float4(0.f, 0.f, 0.f, 0.f);
+    u64        id    = 0;
+    float      d2    = 0.f;
+    bool       found = false;
+    if (valid)
+    {
+        const u64 key = w.qkey[q];
+        const u32 br  = (u32)key;
+        found         = br != 0xFFFFFFFFu;
+        if (found)
+        {
+            const float4 p = w.qpt[q];
+            int          cx, cy, cz;
+            Tr::to_index(p.x, inv, cx), Tr::to_index(p.y, inv, cy), Tr::to_index(p.z, inv, cz);
+            const int b = (int)(br >> 5), slot = (int)(br & 31);
+            const int x = cx + b / 9 - 1, y = cy + (b / 3) % 3 - 1, z = cz + b % 3 - 1;
+            u32       vid = 0, c;
+            probe_ro(m.table, m.mask, pack_key(x, y, z), vid, c);
+            t  = __ldg(m.pts + (size_t)vid * CAP + slot);
+            id = plain_id<Tr::SLOT_BITS>(x, y, z, slot);
+            d2 = __uint_as_float((u32)(key >> 32));
+        }
+        out.found[q] = found ? 1 : 0;
+        out.d2[q]    = d2;
+        out.id[q]    = id;
+    }
+    // xyz is an array of structs: transpose through shuffles so the warp writes its 96 floats as three fully coalesced
+    // 128-byte stores (matters most when `out` is mapped host memory: whole PCIe write bursts)
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {
+        const int   ww = 32 * k + lane, src = ww / 3, c = ww - 3 * src;
+        const float vx = __shfl_sync(MMG_FULL, t.x, src), vy = __shfl_sync(MMG_FULL, t.y, src), vz = __shfl_sync(MMG_FULL, t.z, src);
+        if (q0 + (u32)src < n) out.xyz[3 * (size_t)q0 + ww] = c == 0 ? vx : (c == 1 ? vy : vz);
+    }
+}
+}  // namespace mmg

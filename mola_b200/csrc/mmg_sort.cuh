@@ -5,9 +5,11 @@
 #pragma once
 #include "mmg_device.cuh"
 
+#include <atomic>
+
 namespace mmg
 {
-extern unsigned long long g_launches;  // kernels launched by this library (mmg_kernel_launch_count)
+extern std::atomic<unsigned long long> g_launches;  // kernels launched by this library (mmg_kernel_launch_count)
 #define MMG_LAUNCH(kernel, grid, block, smem, stream, ...)              \
     do {                                                                \
         kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);     \

@@ -97,24 +97,24 @@ int sv_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, siz
         set_error("nn_radius_search batch produced %llu hits (limit 2^31-1): split the batch", (unsigned long long)total);
         return MMG_ERR_INVALID_ARG;
     }
-    m->rad_total = total;
+    rad_result().total = total;
     char* hb     = (char*)m->scratch_get(S_RHITS, std::max<u64>(total, 1) * 24);
     if (!hb) return MMG_ERR_OUT_OF_MEM;
-    m->rad_id = (u64*)hb, m->rad_xyz = (float*)(hb + total * 8), m->rad_d2 = (float*)(hb + total * 20);
+    rad_result().id = (u64*)hb, rad_result().xyz = (float*)(hb + total * 8), rad_result().d2 = (float*)(hb + total * 20);
     if (total)
     {
         u32* qid = nullptr;
         if (maxp != 0 && !(qid = (u32*)m->scratch_get(S_QID, total * sizeof(u32)))) return MMG_ERR_OUT_OF_MEM;
-        MMG_LAUNCH((k_radius_sv<1>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, r2, r, mean, counts, offs, m->rad_xyz, m->rad_d2,
-                   m->rad_id, qid);
+        MMG_LAUNCH((k_radius_sv<1>), g, 128, 0, st, m->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, m->inv, r2, r, mean, counts, offs, rad_result().xyz, rad_result().d2,
+                   rad_result().id, qid);
         if (maxp != 0)
         {
             u32* sbuf = (u32*)m->scratch_get(S_HSORT, sort_scratch_words(total) * sizeof(u32));
             u32* work = (u32*)m->scratch_get(S_HWORK, hits_work_words(total, n) * sizeof(u32));
             if (!sbuf || !work) return MMG_ERR_OUT_OF_MEM;
-            const float* sxyz = m->rad_xyz;
-            const float* sd2  = m->rad_d2;
-            const u64*   sid  = m->rad_id;
+            const float* sxyz = rad_result().xyz;
+            const float* sd2  = rad_result().d2;
+            const u64*   sid  = rad_result().id;
             if ((rc = hits_map_semantics(m, (u32)n, (u32)total, qid, nullptr, sort_scratch_at(sbuf, total), work, sxyz, sd2, sid, maxp, offs, &total, st)))
                 return rc;
         }

@@ -264,6 +264,8 @@ int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     const mmg_params& P = m->prm;
     int               rc;
     // eraseGridsFartherThan(:961-1000); the option is held in a float member (:893)
+    const bool no_clearance = (has_robot_pose & MMG_INSERT_NO_CLEARANCE) != 0;
+    has_robot_pose &= MMG_INSERT_ROBOT_POSE;
     if (has_robot_pose && pose12 && P.remove_voxels_farther_than > 0 && s->brow_hi > s->bfree_n)
     {
         const float dist = (float)P.remove_voxels_farther_than;
@@ -306,8 +308,10 @@ int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     const PoseD T = make_pose(pose12);
     MMG_LAUNCH(k_trees_compose, gN, 256, 0, st, dx, dy, dz, N, T, gp);
     const float*   gq = (const float*)gp;
-    if ((rc = launch_trees_nn1(m, gq, gq + 1, gq + 2, n, 4u, T, 0, -1.0f, (uint8_t*)nullptr, (float*)nullptr, d2, (u64*)nullptr, st))) return rc;
-    const float thr = P.minimum_points_clearance * P.minimum_points_clearance;
+    // the public insertPoint() appends without looking at the map (MMG_INSERT_NO_CLEARANCE): every d2 = 0 passes "d2 > -1"
+    if (no_clearance) MMG_CUDA(cudaMemsetAsync(d2, 0, n * sizeof(float), st));
+    else if ((rc = launch_trees_nn1(m, gq, gq + 1, gq + 2, n, 4u, T, 0, -1.0f, (uint8_t*)nullptr, (float*)nullptr, d2, (u64*)nullptr, st))) return rc;
+    const float thr = no_clearance ? -1.0f : P.minimum_points_clearance * P.minimum_points_clearance;
     MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->oob, 0, sizeof(u32), st));
     MMG_LAUNCH(k_trees_flags, gN, 256, 0, st, s->dev, gp, d2, N, thr, flag);
     exclusive_scan<u32, u32>(flag, pos, n, pos + n, bsum, st);
@@ -493,10 +497,10 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
             if ((rc = hits_map_semantics(m, (u32)n, (u32)H, qkey, hseg, ss, work, sxyz, sd2, sid, 0u, qoff, &total, st))) return rc;
         }
         else
-            m->rad_total = 0;
+            rad_result().total = 0;
     }
     else
-        m->rad_total = 0;
+        rad_result().total = 0;
     MMG_CUDA(cudaGetLastError());
     MMG_CUDA(cudaMemcpyAsync(ooff, qoff, (n + 1) * sizeof(u64), mem == MMG_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
     MMG_CUDA(cudaStreamSynchronize(st));

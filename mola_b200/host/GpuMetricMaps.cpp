@@ -86,6 +86,7 @@ GpuPointMapBase& GpuPointMapBase::operator=(GpuPointMapBase&& o) noexcept
 
 void GpuPointMapBase::syncParams() const
 {
+    std::lock_guard<std::mutex> lk(paramsMtx_);
     mmg_params p = pushed_;
     fillParams(p);
     p.voxel_size = size_;
@@ -130,65 +131,132 @@ void GpuPointMapBase::insertPointCloud(const float* xs, const float* ys, const f
     if (rc != MMG_ERR_OUT_OF_RANGE) check(rc);  // out-of-range points are skipped, the rest is inserted
     cachedPoints_.reset();
 }
-void GpuPointMapBase::insertPoint(const mrpt::math::TPoint3Df& pt) { insertPointCloud(&pt.x, &pt.y, &pt.z, 1, std::nullopt, false); }
+void GpuPointMapBase::insertPoint(const mrpt::math::TPoint3Df& pt)
+{   // the reference's public insertPoint(): decimating for the voxel maps, a plain append for SparseTrees (.h:224-234)
+    syncParams();
+    const int rc = mmg_insert_batch(h_, &pt.x, &pt.y, &pt.z, 1, nullptr, MMG_INSERT_NO_CLEARANCE, MMG_MEM_HOST, nullptr);
+    if (rc != MMG_ERR_OUT_OF_RANGE) check(rc);
+    cachedPoints_.reset();
+}
+
+void GpuPointMapBase::insertObservationPoints(const float* xs, const float* ys, const float* zs, size_t n,
+                                              const std::optional<const mrpt::poses::CPose3D>& robotPose, bool pointByPoint)
+{
+    // The reference composes every point with robotPose3D, which is the identity when no robot pose is given
+    // (HashedVoxelPointCloud.cpp:297-331); the eviction only runs with a given pose (:300-327).
+    syncParams();
+    double T[12];
+    pose12(robotPose ? mrpt::poses::CPose3D(*robotPose) : mrpt::poses::CPose3D(), T);
+    int flags = robotPose ? MMG_INSERT_ROBOT_POSE : 0;
+    // SparseTrees: the branches that loop over the public insertPoint() append without the clearance test
+    // (SparseTreesPointCloud.cpp:349-356 against :381-383, :400-401); for the voxel maps both forms decimate alike
+    if (pointByPoint && kind_ == MMG_SPARSE_TREES) flags |= MMG_INSERT_NO_CLEARANCE;
+    const int rc = mmg_insert_batch(h_, xs, ys, zs, n, T, flags, MMG_MEM_HOST, nullptr);
+    if (rc != MMG_ERR_OUT_OF_RANGE) check(rc);  // out-of-range points are skipped, the rest is inserted
+    cachedPoints_.reset();
+}
 
 bool GpuPointMapBase::internal_insertObservation(const mrpt::obs::CObservation& obs, const std::optional<const mrpt::poses::CPose3D>& robotPose)
-{  // HashedVoxelPointCloud.cpp:289-432: the point cloud is composed with robotPose + sensorPose
+{
+    // HashedVoxelPointCloud.cpp:289-432, SparseVoxelPointCloud.cpp:363-480, SparseTreesPointCloud.cpp:289-410.
+    // Every class composes its points with the ROBOT pose only: a 2-D scan's auxiliary map and an unprojected range
+    // image already are in the robot frame (they include sensorPose), while points3D, a Velodyne cloud and a
+    // CObservationPointCloud are sensor-frame points whose sensorPose the reference ignores on insertion.
     using namespace mrpt::obs;
-    const mrpt::poses::CPose3D robot = robotPose ? mrpt::poses::CPose3D(*robotPose) : mrpt::poses::CPose3D();
-    if (auto* o = dynamic_cast<const CObservationPointCloud*>(&obs); o)
+    // which branches loop over insertPoint() (true) and which call internal_insertPointCloud3D (false)
+    const bool trees = kind_ == MMG_SPARSE_TREES;
+    if (auto* o = dynamic_cast<const CObservation2DRangeScan*>(&obs); o)
     {
-        if (!o->pointcloud) return false;
-        const auto& xs = o->pointcloud->getPointsBufferRef_x();
-        const auto& ys = o->pointcloud->getPointsBufferRef_y();
-        const auto& zs = o->pointcloud->getPointsBufferRef_z();
-        // eviction uses the robot pose (:305-326), the points use robot (+) sensor
-        syncParams();
-        double rp[12], sp[12];
-        pose12(robot, rp);
-        pose12(robot + o->sensorPose, sp);
-        if (robotPose) check(mmg_insert_batch(h_, nullptr, nullptr, nullptr, 0, rp, 1, MMG_MEM_HOST, nullptr));
-        const int rc = mmg_insert_batch(h_, xs.data(), ys.data(), zs.data(), xs.size(), sp, 0, MMG_MEM_HOST, nullptr);
-        if (rc != MMG_ERR_OUT_OF_RANGE) check(rc);
-        cachedPoints_.reset();
-        return true;
+        const auto* scanPoints = o->buildAuxPointsMap<mrpt::maps::CPointsMap>();
+        // "if (scanPoints->empty()) return 0;" comes after the eviction in the reference: run it for its side effect
+        const auto& xs = scanPoints->getPointsBufferRef_x();
+        const auto& ys = scanPoints->getPointsBufferRef_y();
+        const auto& zs = scanPoints->getPointsBufferRef_z();
+        insertObservationPoints(xs.data(), ys.data(), zs.data(), xs.size(), robotPose, false);
+        return !scanPoints->empty();
+    }
+    if (auto* o = dynamic_cast<const CObservation3DRangeScan*>(&obs); o)
+    {
+        if (o->hasPoints3D)
+        {
+            insertObservationPoints(o->points3D_x.data(), o->points3D_y.data(), o->points3D_z.data(), o->points3D_x.size(), robotPose, true);
+            return true;
+        }
+        if (o->hasRangeImage)
+        {
+            T3DPointsProjectionParams pp;
+            pp.takeIntoAccountSensorPoseOnRobot = true;
+            mrpt::maps::CSimplePointsMap pointMap;
+            const_cast<CObservation3DRangeScan*>(o)->unprojectInto(pointMap, pp);
+            const auto& xs = pointMap.getPointsBufferRef_x();
+            const auto& ys = pointMap.getPointsBufferRef_y();
+            const auto& zs = pointMap.getPointsBufferRef_z();
+            insertObservationPoints(xs.data(), ys.data(), zs.data(), xs.size(), robotPose, false);
+            return true;
+        }
+        insertObservationPoints(nullptr, nullptr, nullptr, 0, robotPose, false);  // the eviction has already run there
+        return false;
     }
     if (auto* o = dynamic_cast<const CObservationVelodyneScan*>(&obs); o)
     {
+        if (!o->point_cloud.size()) const_cast<CObservationVelodyneScan*>(o)->generatePointCloud();
         const auto& pc = o->point_cloud;
-        if (!pc.size()) return false;
-        syncParams();
-        double rp[12], sp[12];
-        pose12(robot, rp);
-        pose12(robot + o->sensorPose, sp);
-        if (robotPose) check(mmg_insert_batch(h_, nullptr, nullptr, nullptr, 0, rp, 1, MMG_MEM_HOST, nullptr));
-        const int rc = mmg_insert_batch(h_, pc.x.data(), pc.y.data(), pc.z.data(), pc.size(), sp, 0, MMG_MEM_HOST, nullptr);
-        if (rc != MMG_ERR_OUT_OF_RANGE) check(rc);
-        cachedPoints_.reset();
+        insertObservationPoints(pc.x.data(), pc.y.data(), pc.z.data(), pc.x.size(), robotPose, !trees);
         return true;
     }
-    return false;  // unknown observation class (:426-432)
+    if (auto* o = dynamic_cast<const CObservationPointCloud*>(&obs); o)
+    {
+        if (!o->pointcloud) insertObservationPoints(nullptr, nullptr, nullptr, 0, robotPose, false);
+        ASSERT_(o->pointcloud);
+        const auto& xs = o->pointcloud->getPointsBufferRef_x();
+        const auto& ys = o->pointcloud->getPointsBufferRef_y();
+        const auto& zs = o->pointcloud->getPointsBufferRef_z();
+        insertObservationPoints(xs.data(), ys.data(), zs.data(), xs.size(), robotPose, !trees);
+        return true;
+    }
+    insertObservationPoints(nullptr, nullptr, nullptr, 0, robotPose, false);  // unknown class (:426-432): eviction only
+    return false;
 }
 
 bool GpuPointMapBase::internal_canComputeObservationLikelihood(const mrpt::obs::CObservation& obs) const
-{
-    return dynamic_cast<const mrpt::obs::CObservationPointCloud*>(&obs) != nullptr ||
-           dynamic_cast<const mrpt::obs::CObservationVelodyneScan*>(&obs) != nullptr;
+{  // HashedVoxelPointCloud.cpp:548-556
+    return dynamic_cast<const mrpt::obs::CObservation2DRangeScan*>(&obs) != nullptr ||
+           dynamic_cast<const mrpt::obs::CObservationVelodyneScan*>(&obs) != nullptr ||
+           dynamic_cast<const mrpt::obs::CObservationPointCloud*>(&obs) != nullptr;
 }
 double GpuPointMapBase::internal_computeObservationLikelihood(const mrpt::obs::CObservation& obs, const mrpt::poses::CPose3D& takenFrom) const
-{  // :434-546
+{  // HashedVoxelPointCloud.cpp:434-507: a 2-D scan's points are in the robot frame (takenFrom alone), the other two
+   // classes hold sensor-frame points (takenFrom + sensorPose)
+    using namespace mrpt::obs;
+    if (isEmpty()) return 0;
     const float *xs = nullptr, *ys = nullptr, *zs = nullptr;
     size_t       n  = 0;
-    if (auto* o = dynamic_cast<const mrpt::obs::CObservationPointCloud*>(&obs); o && o->pointcloud)
+    mrpt::poses::CPose3D pc_in_map = takenFrom;
+    if (auto* s = dynamic_cast<const CObservation2DRangeScan*>(&obs); s)
+    {
+        const auto* scanPoints = s->buildAuxPointsMap<mrpt::maps::CPointsMap>();
+        xs = scanPoints->getPointsBufferRef_x().data(), ys = scanPoints->getPointsBufferRef_y().data(), zs = scanPoints->getPointsBufferRef_z().data();
+        n  = scanPoints->size();
+    }
+    else if (auto* v = dynamic_cast<const CObservationVelodyneScan*>(&obs); v)
+    {
+        if (!v->point_cloud.size()) const_cast<CObservationVelodyneScan*>(v)->generatePointCloud();
+        xs = v->point_cloud.x.data(), ys = v->point_cloud.y.data(), zs = v->point_cloud.z.data(), n = v->point_cloud.size();
+        pc_in_map = takenFrom + v->sensorPose;
+    }
+    else if (auto* o = dynamic_cast<const CObservationPointCloud*>(&obs); o)
+    {
+        ASSERT_(o->pointcloud);
         xs = o->pointcloud->getPointsBufferRef_x().data(), ys = o->pointcloud->getPointsBufferRef_y().data(),
         zs = o->pointcloud->getPointsBufferRef_z().data(), n = o->pointcloud->size();
-    else if (auto* v = dynamic_cast<const mrpt::obs::CObservationVelodyneScan*>(&obs); v)
-        xs = v->point_cloud.x.data(), ys = v->point_cloud.y.data(), zs = v->point_cloud.z.data(), n = v->point_cloud.size();
+        pc_in_map = takenFrom + o->sensorPose;
+    }
     else
         return 0;
+    if (!n) return 0;
     syncParams();
     double T[12], out = 0;
-    pose12(takenFrom + obs.sensorPose, T);
+    pose12(pc_in_map, T);
     check(mmg_likelihood(h_, xs, ys, zs, n, T, &out, MMG_MEM_HOST, nullptr));
     return out;
 }

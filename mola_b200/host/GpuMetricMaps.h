@@ -26,6 +26,7 @@
 #include <cstdint>
 #include <functional>
 #include <memory>
+#include <mutex>
 #include <optional>
 #include <string>
 #include <vector>
@@ -58,7 +59,8 @@ class GpuPointMapBase : public mrpt::maps::CMetricMap, public mrpt::maps::Neares
     GpuPointMapBase(GpuPointMapBase&& o) noexcept;
     GpuPointMapBase& operator=(GpuPointMapBase&& o) noexcept;
 
-    /** Insert one point (1-element batch; use insertPointCloud for scans). */
+    /** Insert one point (1-element batch; use insertPointCloud for scans). SparseTrees: appended without the
+     *  clearance test, like the reference's public insertPoint(). */
     void insertPoint(const mrpt::math::TPoint3Df& pt);
     /** Compose with `pose` (identity if empty) and insert in input order; a given pose also
      *  triggers the far-voxel / far-block eviction (HashedVoxelPointCloud.cpp:289-331). */
@@ -124,6 +126,10 @@ class GpuPointMapBase : public mrpt::maps::CMetricMap, public mrpt::maps::Neares
     bool internal_insertObservation(const mrpt::obs::CObservation& obs, const std::optional<const mrpt::poses::CPose3D>& robotPose) override;
     double internal_computeObservationLikelihood(const mrpt::obs::CObservation& obs, const mrpt::poses::CPose3D& takenFrom) const override;
     bool   internal_canComputeObservationLikelihood(const mrpt::obs::CObservation& obs) const override;
+    /** One branch of internal_insertObservation: eviction (with a robot pose), compose with the robot pose, insert.
+     *  pointByPoint = the reference loops over insertPoint() there instead of calling internal_insertPointCloud3D. */
+    void insertObservationPoints(const float* xs, const float* ys, const float* zs, size_t n,
+                                 const std::optional<const mrpt::poses::CPose3D>& robotPose, bool pointByPoint);
     /** Writes the class's current option members into p. */
     virtual void fillParams(mmg_params& p) const = 0;
     virtual const char* mapName() const          = 0;
@@ -136,6 +142,7 @@ class GpuPointMapBase : public mrpt::maps::CMetricMap, public mrpt::maps::Neares
     float            size_;
     mutable mmg_map* h_ = nullptr;
     mutable mmg_params pushed_{};
+    mutable std::mutex paramsMtx_;  // const queries from several threads all pass through syncParams()
     mutable std::shared_ptr<mrpt::maps::CSimplePointsMap> cachedPoints_;
 };
 

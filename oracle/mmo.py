@@ -47,6 +47,15 @@ def have_reference():
     return os.path.exists(REF_PATH)
 
 
+def checker():
+    """The CPU twin the parity tests compare against: the reference's own code (oracle/_ref, reference sources
+    compiled against the MRPT stand-in) wherever it was built, the port otherwise. MMO_CHECKER=port|reference overrides."""
+    w = os.environ.get("MMO_CHECKER")
+    if w in ("port", "reference"):
+        return w
+    return "reference" if have_reference() else "port"
+
+
 def _f(a):
     return a.ctypes.data_as(C.POINTER(C.c_float))
 
@@ -61,8 +70,9 @@ def _pose(p):
 class OracleMap:
     """Same surface as mola_b200.maps._Map, on the CPU."""
 
-    def __init__(self, kind, size, which="port", **opts):
-        self.lib = load(which)
+    def __init__(self, kind, size, which=None, **opts):
+        self.which = which or checker()
+        self.lib = load(self.which)
         self.kind = kind
         self.p = Params(voxel_size=size, max_points_per_voxel=0, remove_voxels_farther_than=0.0,
                         min_distance_between_points=0.0, minimum_points_clearance=0.20, sigma_dist=0.5,

@@ -182,7 +182,11 @@ int mmo_ref_deserialize(void* h, const uint8_t* buf, size_t n)
         return -1;
     }
 }
-void mmo_clear(void* h) { ((Handle*)h)->base()->clear(); }
+// The reference object itself, as the mrpt::maps::CMetricMap* its plugin interface is. The C++ host-class test (built
+// against the same stand-in headers) calls insertObservation / computeObservationLikelihood on it with every
+// observation class and a non-identity sensorPose, next to the same call on the GPU class. Reference library only.
+void* mmo_ref_metric_map(void* h) { return ((Handle*)h)->base(); }
+void  mmo_clear(void* h) { ((Handle*)h)->base()->clear(); }
 void mmo_set_params(void* h, const mmo_params* p) { ((Handle*)h)->apply(*p, false); }
 int  mmo_is_empty(void* h) { return ((Handle*)h)->base()->isEmpty() ? 1 : 0; }
 

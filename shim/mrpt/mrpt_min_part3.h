@@ -88,52 +88,7 @@ class CSimplePointsMap;
 // ----------------------------------------------------------------------- obs
 namespace obs
 {
-class CObservation
-{
-   public:
-    using Ptr = std::shared_ptr<CObservation>;
-    virtual ~CObservation() = default;
-    mrpt::poses::CPose3D sensorPose;
-};
-struct T3DPointsProjectionParams
-{
-    bool takeIntoAccountSensorPoseOnRobot = false;
-};
-class CObservationPointCloud : public CObservation
-{
-   public:
-    std::shared_ptr<mrpt::maps::CPointsMap> pointcloud;
-};
-class CObservation2DRangeScan : public CObservation
-{
-   public:
-    std::shared_ptr<mrpt::maps::CPointsMap> aux;
-    template <class M>
-    const M* buildAuxPointsMap() const
-    {
-        return static_cast<const M*>(aux.get());
-    }
-};
-class CObservation3DRangeScan : public CObservation
-{
-   public:
-    bool               hasPoints3D = false, hasRangeImage = false;
-    std::vector<float> points3D_x, points3D_y, points3D_z;
-    template <class M>
-    void unprojectInto(M&, const T3DPointsProjectionParams&)
-    {
-    }
-};
-class CObservationVelodyneScan : public CObservation
-{
-   public:
-    struct TPointCloud
-    {
-        std::vector<float> x, y, z;
-        size_t             size() const { return x.size(); }
-    } point_cloud;
-    void generatePointCloud() {}
-};
+class CObservation;  // defined after the maps (the 2-D scan builds a CSimplePointsMap)
 }  // namespace obs
 
 // ---------------------------------------------------------------------- maps
@@ -297,7 +252,8 @@ class CPointsMap : public CMetricMap
 
    protected:
     void internal_clear() override { x_.clear(), y_.clear(), z_.clear(); }
-    bool internal_insertObservation(const mrpt::obs::CObservation&, const std::optional<const mrpt::poses::CPose3D>&) override { return false; }
+    // 2-D range scans only (what the reference's tests insert into a CSimplePointsMap); defined after the observations
+    bool internal_insertObservation(const mrpt::obs::CObservation&, const std::optional<const mrpt::poses::CPose3D>&) override;
     std::vector<float> x_, y_, z_;
 };
 class CSimplePointsMap : public CPointsMap
@@ -308,6 +264,142 @@ class CSimplePointsMap : public CPointsMap
     const char* className() const override { return "CSimplePointsMap"; }
 };
 }  // namespace maps
+
+// ----------------------------------------------------------------------- obs
+// Observation classes with the members the map classes touch, shaped like upstream MRPT 2.x: `sensorPose` is a member
+// of every DERIVED class (the base only has the virtual getSensorPose()), a 2-D scan carries ranges + validity and
+// builds its auxiliary points map in the ROBOT frame (sensor pose applied, like CPointsMap::loadFromRangeScan without a
+// robot pose), a 3-D range scan unprojects its depth image with a pinhole model and, when asked, applies the sensor
+// pose, a Velodyne scan generates its cloud from (azimuth, elevation, range) returns in the sensor frame. The
+// arithmetic of these conversions is this stand-in's own (double composePoint, float sin/cos): unpinned against
+// upstream MRPT, but shared by the reference classes and the GPU classes, which is what the parity tests need.
+namespace obs
+{
+class CObservation
+{
+   public:
+    using Ptr = std::shared_ptr<CObservation>;
+    virtual ~CObservation()                                     = default;
+    virtual void getSensorPose(mrpt::poses::CPose3D& out) const = 0;
+};
+struct T3DPointsProjectionParams
+{
+    bool takeIntoAccountSensorPoseOnRobot = false;
+};
+class CObservationPointCloud : public CObservation
+{
+   public:
+    std::shared_ptr<mrpt::maps::CPointsMap> pointcloud;
+    mrpt::poses::CPose3D                    sensorPose;
+    void getSensorPose(mrpt::poses::CPose3D& out) const override { out = sensorPose; }
+};
+class CObservation2DRangeScan : public CObservation
+{
+   public:
+    float                aperture    = 3.14159265358979f;  // field of view, radians
+    bool                 rightToLeft = true;               // scan direction (counter-clockwise seen from above)
+    float                maxRange    = 80.0f;
+    mrpt::poses::CPose3D sensorPose;
+    void getSensorPose(mrpt::poses::CPose3D& out) const override { out = sensorPose; }
+    void resizeScan(size_t n) { ranges_.assign(n, 0.f), valid_.assign(n, 0), aux_.reset(); }
+    size_t getScanSize() const { return ranges_.size(); }
+    float  getScanRange(size_t i) const { return ranges_[i]; }
+    bool   getScanRangeValidity(size_t i) const { return valid_[i] != 0; }
+    void   setScanRange(size_t i, float r) { ranges_[i] = r, aux_.reset(); }
+    void   setScanRangeValidity(size_t i, bool v) { valid_[i] = v ? 1 : 0, aux_.reset(); }
+    /** The scan as points in the robot frame (cached), CObservation2DRangeScan::buildAuxPointsMap. */
+    template <class M>
+    const M* buildAuxPointsMap(const void* = nullptr) const
+    {
+        if (!aux_)
+        {
+            auto         pm = mrpt::maps::CSimplePointsMap::Create();
+            const size_t n  = ranges_.size();
+            const float  a0 = rightToLeft ? -0.5f * aperture : 0.5f * aperture;
+            const float  da = n > 1 ? (rightToLeft ? aperture : -aperture) / (float)(n - 1) : 0.f;
+            for (size_t i = 0; i < n; i++)
+            {
+                if (!valid_[i]) continue;
+                const float a = a0 + da * (float)i, r = ranges_[i];
+                pm->insertPoint(sensorPose.composePoint(mrpt::math::TPoint3Df(r * std::cos(a), r * std::sin(a), 0.f)));
+            }
+            aux_ = pm;
+        }
+        return static_cast<const M*>(aux_.get());
+    }
+
+   private:
+    std::vector<float>                                     ranges_;
+    std::vector<uint8_t>                                   valid_;
+    mutable std::shared_ptr<mrpt::maps::CSimplePointsMap> aux_;
+};
+class CObservation3DRangeScan : public CObservation
+{
+   public:
+    bool               hasPoints3D = false, hasRangeImage = false;
+    std::vector<float> points3D_x, points3D_y, points3D_z;  // sensor frame
+    // depth image (metres along the sensor's +X axis, 0 = no return) and its pinhole intrinsics
+    size_t             rangeRows = 0, rangeCols = 0;
+    std::vector<float> rangeImage;
+    struct
+    {
+        float fx = 1, fy = 1, cx = 0, cy = 0;
+    } cameraParams;
+    mrpt::poses::CPose3D sensorPose;
+    void getSensorPose(mrpt::poses::CPose3D& out) const override { out = sensorPose; }
+    /** x = depth, y = (cx - col) * depth / fx, z = (cy - row) * depth / fy; optionally moved to the robot frame. */
+    template <class M>
+    void unprojectInto(M& dest, const T3DPointsProjectionParams& pp)
+    {
+        for (size_t r = 0; r < rangeRows; r++)
+            for (size_t c = 0; c < rangeCols; c++)
+            {
+                const float d = rangeImage[r * rangeCols + c];
+                if (!(d > 0.f)) continue;
+                const mrpt::math::TPoint3Df l(d, (cameraParams.cx - (float)c) * d / cameraParams.fx, (cameraParams.cy - (float)r) * d / cameraParams.fy);
+                if (pp.takeIntoAccountSensorPoseOnRobot) dest.insertPoint(sensorPose.composePoint(l));
+                else dest.insertPoint(l);
+            }
+    }
+};
+class CObservationVelodyneScan : public CObservation
+{
+   public:
+    struct TPointCloud
+    {
+        std::vector<float> x, y, z;
+        size_t             size() const { return x.size(); }
+        void               clear() { x.clear(), y.clear(), z.clear(); }
+    } point_cloud;
+    /** Raw returns (stand-in for scan_packets): azimuth, elevation (radians) and range (metres; <= 0 = none). */
+    std::vector<float>   raw_azimuth, raw_elevation, raw_range;
+    mrpt::poses::CPose3D sensorPose;
+    void getSensorPose(mrpt::poses::CPose3D& out) const override { out = sensorPose; }
+    /** Sensor-frame points from the raw returns. */
+    void generatePointCloud()
+    {
+        point_cloud.clear();
+        for (size_t i = 0; i < raw_range.size(); i++)
+        {
+            const float r = raw_range[i];
+            if (!(r > 0.f)) continue;
+            const float ce = std::cos(raw_elevation[i]);
+            point_cloud.x.push_back(r * ce * std::cos(raw_azimuth[i]));
+            point_cloud.y.push_back(r * ce * std::sin(raw_azimuth[i]));
+            point_cloud.z.push_back(r * std::sin(raw_elevation[i]));
+        }
+    }
+};
+}  // namespace obs
+inline bool maps::CPointsMap::internal_insertObservation(const mrpt::obs::CObservation& obs, const std::optional<const mrpt::poses::CPose3D>& robotPose)
+{
+    const auto* s = dynamic_cast<const mrpt::obs::CObservation2DRangeScan*>(&obs);
+    if (!s) return false;
+    const auto*                aux = s->buildAuxPointsMap<CPointsMap>();
+    const mrpt::poses::CPose3D T   = robotPose ? mrpt::poses::CPose3D(*robotPose) : mrpt::poses::CPose3D();
+    for (size_t i = 0; i < aux->size(); i++) insertPoint(T.composePoint(mrpt::math::TPoint3Df(aux->x_[i], aux->y_[i], aux->z_[i])));
+    return true;
+}
 }  // namespace mrpt
 
 // Map-definition plumbing (mrpt/maps/metric_map_types.h), reduced to what the classes need.

@@ -11,8 +11,28 @@
 #include <map>
 #include <tuple>
 
+#include <mrpt/obs/CObservation2DRangeScan.h>
+#include <mrpt/obs/CObservation3DRangeScan.h>
+#include <mrpt/obs/CObservationVelodyneScan.h>
+
+#include <thread>
+#include <type_traits>
+
 #include "../../mola_b200/host/GpuMetricMaps.h"
 #include "../../oracle/mmo.h"
+
+// copy / move traits of the three GPU classes, as the reference asserts for its own (tests/test-serialization.cpp:35-51)
+template <typename T>
+struct TraitsTest
+{
+    static_assert(std::is_move_constructible<T>(), "Can't move construct");
+    static_assert(std::is_copy_constructible<T>(), "Can't copy construct");
+    static_assert(std::is_move_assignable<T>(), "Can't move assign");
+    static_assert(std::is_copy_assignable<T>(), "Can't copy assign");
+};
+template struct TraitsTest<MOLA_B200_NAMESPACE::HashedVoxelPointCloud>;
+template struct TraitsTest<MOLA_B200_NAMESPACE::SparseVoxelPointCloud>;
+template struct TraitsTest<MOLA_B200_NAMESPACE::SparseTreesPointCloud>;
 
 namespace mg = MOLA_B200_NAMESPACE;
 using mrpt::math::TPoint3Df;
@@ -61,6 +81,7 @@ struct Oracle
     // reference library only (nullptr with the port): archives of the reference classes themselves
     size_t (*ref_serialize)(void*, uint8_t*, size_t)        = nullptr;
     int (*ref_deserialize)(void*, const uint8_t*, size_t)   = nullptr;
+    void* (*ref_metric_map)(void*)                          = nullptr;  // the reference object as its CMetricMap*
     explicit Oracle(const char* path)
     {
         h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
@@ -73,7 +94,7 @@ struct Oracle
         S(create, "mmo_create"), S(destroy, "mmo_destroy"), S(insert, "mmo_insert"), S(nn_single, "mmo_nn_single"), S(nn_multi, "mmo_nn_multi");
         S(nn_radius, "mmo_nn_radius"), S(nn_radius_fetch, "mmo_nn_radius_fetch"), S(likelihood, "mmo_likelihood"), S(bbox, "mmo_bbox");
         S(num_voxels, "mmo_num_voxels"), S(num_points, "mmo_num_points"), S(row_capacity, "mmo_row_capacity"), S(export_, "mmo_export");
-        S(ref_serialize, "mmo_ref_serialize"), S(ref_deserialize, "mmo_ref_deserialize");
+        S(ref_serialize, "mmo_ref_serialize"), S(ref_deserialize, "mmo_ref_deserialize"), S(ref_metric_map, "mmo_ref_metric_map");
 #undef S
     }
 };
@@ -454,6 +475,286 @@ static void run_case(Oracle& O, const Case& c)
     O.destroy(o);
 }
 
+
+// =====================================================================================================================
+// Every observation class of internal_insertObservation, with a NON-identity sensorPose, through CMetricMap's own
+// insertObservation / computeObservationLikelihood on the GPU class and on the reference class side by side
+// (HashedVoxelPointCloud.cpp:289-507, SparseVoxelPointCloud.cpp:363-600, SparseTreesPointCloud.cpp:289-528).
+static int g_observation_checks = 0;
+static const mrpt::poses::CPose3D kSensorPose = mrpt::poses::CPose3D::FromXYZYawPitchRoll(0.30, -0.20, 0.50, 0.20, 0.05, -0.03);
+
+// a 2-D scan of a 12 x 8 m room seen from its middle, a few invalid rays (stands in for MRPT's stock example scan)
+static void make_scan2d(mrpt::obs::CObservation2DRangeScan& s, int n = 361, float jitter = 0.f)
+{
+    s.aperture    = 3.14159265f;
+    s.rightToLeft = true;
+    s.sensorPose  = kSensorPose;
+    s.resizeScan(n);
+    for (int i = 0; i < n; i++)
+    {
+        const float a  = -0.5f * s.aperture + s.aperture * (float)i / (float)(n - 1);
+        const float ca = std::cos(a), sa = std::sin(a);
+        const float rx = std::fabs(ca) > 1e-3f ? 6.0f / std::fabs(ca) : 1e9f, ry = std::fabs(sa) > 1e-3f ? 4.0f / std::fabs(sa) : 1e9f;
+        s.setScanRange(i, std::min(rx, ry) + jitter * (frand() - 0.5f));
+        s.setScanRangeValidity(i, i % 17 != 3);
+    }
+}
+struct UnknownObservation : public mrpt::obs::CObservation
+{
+    void getSensorPose(mrpt::poses::CPose3D& out) const override { out = mrpt::poses::CPose3D(); }
+};
+static void run_observations(Oracle& O, const Case& c)
+{
+    using namespace mrpt::obs;
+    using mrpt::poses::CPose3D;
+    std::printf("observations %s size=%.2f\n", c.cls, c.size);
+    auto  mapPtr = create_from_definition(c);
+    auto* m      = dynamic_cast<mg::GpuPointMapBase*>(mapPtr.get());
+    void* o      = O.create(c.kind, &c.prm);
+    auto* ref    = O.ref_metric_map ? static_cast<mrpt::maps::CMetricMap*>(O.ref_metric_map(o)) : nullptr;
+    if (!ref)
+    {
+        std::printf("  (port library loaded: the observation classes need the reference build, skipped)\n");
+        O.destroy(o);
+        return;
+    }
+    auto both = [&](const CObservation& obs, const CPose3D* pose, const char* what) {
+        const bool a = pose ? mapPtr->insertObservation(obs, *pose) : mapPtr->insertObservation(obs);
+        const bool b = pose ? ref->insertObservation(obs, *pose) : ref->insertObservation(obs);
+        CHECK(a == b);
+        const int before = g_fail;
+        check_same_contents(*m, O, o);
+        if (g_fail != before) std::printf("   ^ after %s\n", what);
+        g_observation_checks++;
+        return a;
+    };
+    auto R = [](int k) { return CPose3D::FromXYZYawPitchRoll(3.0 * k, 0.4 * k, 1.2, 0.1 * k, 0.02, -0.01); };
+    // the reference's basic-ops test (tests/test-mola_metric_maps_hashedvoxels.cpp:35-42): empty, insertPoint, not empty
+    CHECK(mapPtr->isEmpty());
+    m->insertPoint({1.0f, 2.0f, 3.0f});
+    CHECK(!mapPtr->isEmpty());
+    mapPtr->clear();
+
+    CObservation2DRangeScan scan;
+    make_scan2d(scan);
+    const CPose3D r0 = R(0), r1 = R(1), r2 = R(2), r3 = R(3);
+    CHECK(both(scan, &r0, "2D scan, robot pose"));
+    CHECK(both(scan, nullptr, "2D scan, no pose"));
+    CObservation2DRangeScan none;
+    none.resizeScan(10);  // every ray invalid: empty auxiliary map -> false
+    CHECK(!both(none, &r0, "empty 2D scan"));
+
+    CObservation3DRangeScan p3;
+    p3.sensorPose  = kSensorPose;
+    p3.hasPoints3D = true;
+    {
+        const auto pc = make_scan(3000);
+        p3.points3D_x = pc->getPointsBufferRef_x(), p3.points3D_y = pc->getPointsBufferRef_y(), p3.points3D_z = pc->getPointsBufferRef_z();
+    }
+    CHECK(both(p3, &r1, "3D scan, points3D"));
+    CHECK(both(p3, &r1, "3D scan, points3D again (SparseTrees: no clearance test on this branch)"));
+    CObservation3DRangeScan ri;
+    ri.sensorPose    = kSensorPose;
+    ri.hasRangeImage = true;
+    ri.rangeRows = 48, ri.rangeCols = 64;
+    ri.cameraParams.fx = ri.cameraParams.fy = 60.f, ri.cameraParams.cx = 32.f, ri.cameraParams.cy = 24.f;
+    for (size_t i = 0; i < ri.rangeRows * ri.rangeCols; i++) ri.rangeImage.push_back(i % 11 == 5 ? 0.f : 2.0f + 6.0f * frand());
+    CHECK(both(ri, &r2, "3D scan, range image"));
+    CObservation3DRangeScan nothing;
+    CHECK(!both(nothing, &r2, "3D scan without data"));
+
+    CObservationVelodyneScan vraw;
+    vraw.sensorPose = kSensorPose;
+    for (int i = 0; i < 20000; i++)
+    {
+        vraw.raw_azimuth.push_back(6.2831853f * frand()), vraw.raw_elevation.push_back(-0.4f + 0.5f * frand());
+        vraw.raw_range.push_back(i % 13 == 7 ? 0.f : 3.0f + 27.0f * frand());
+    }
+    CHECK(both(vraw, &r3, "Velodyne scan, generatePointCloud()"));
+    CHECK(vraw.point_cloud.size() > 15000);
+    CObservationVelodyneScan vpc;
+    vpc.sensorPose = kSensorPose;
+    {
+        const auto pc = make_scan(4000);
+        vpc.point_cloud.x = pc->getPointsBufferRef_x(), vpc.point_cloud.y = pc->getPointsBufferRef_y(), vpc.point_cloud.z = pc->getPointsBufferRef_z();
+    }
+    CHECK(both(vpc, nullptr, "Velodyne scan, given cloud, no pose"));
+
+    CObservationPointCloud pcl;
+    pcl.sensorPose = kSensorPose;
+    pcl.pointcloud = make_scan(5000);
+    const CPose3D far = CPose3D::FromXYZYawPitchRoll(40.0, 2.0, 1.2, 0.7, 0.0, 0.0);  // evicts when the case has a far limit
+    CHECK(both(pcl, &far, "point cloud, far pose"));
+    UnknownObservation unk;
+    CHECK(!both(unk, &r0, "unknown observation class (eviction only)"));
+    CObservationPointCloud nullpc;
+    CHECK_THROWS(mapPtr->insertObservation(nullpc, r0));  // ASSERT_(o.pointcloud)
+    CHECK_THROWS(ref->insertObservation(nullpc, r0));
+    check_same_contents(*m, O, o);
+
+    // likelihood: 2-D scan = takenFrom alone, the sensor-frame classes = takenFrom + sensorPose
+    CObservation2DRangeScan scanq;
+    make_scan2d(scanq, 361, 0.04f);
+    const CPose3D            guess = CPose3D::FromXYZYawPitchRoll(0.05, -0.02, 1.21, 0.01, 0.02, -0.01);
+    const CObservation*      lik[] = {&scanq, &vraw, &pcl, &p3, &unk};
+    for (const CObservation* ob : lik)
+    {
+        CHECK(mapPtr->canComputeObservationLikelihood(*ob) == ref->canComputeObservationLikelihood(*ob));
+        if (c.kind == 1 && ref->canComputeObservationLikelihood(*ob))
+        {   // nn_single_search throws for this map type, and so does the likelihood built on it
+            CHECK_THROWS((void)mapPtr->computeObservationLikelihood(*ob, guess));
+            CHECK_THROWS((void)ref->computeObservationLikelihood(*ob, guess));
+            continue;
+        }
+        const double a = mapPtr->computeObservationLikelihood(*ob, guess), b = ref->computeObservationLikelihood(*ob, guess);
+        CHECK(std::abs(a - b) <= 1e-9 * std::abs(b));
+        g_observation_checks++;
+    }
+    CHECK(c.kind == 1 || mapPtr->computeObservationLikelihood(scanq, guess) < 0);
+    O.destroy(o);
+}
+
+// The reference's own test scenarios on the GPU classes (MRPT's stock example scan is not on this image: a synthetic
+// 2-D scan takes its place, and the 267-point / 96-voxel constants become "the same numbers as the reference class").
+static void replay_reference_tests(Oracle& O)
+{
+    using namespace mrpt::obs;
+    std::printf("reference test scenarios\n");
+    auto P = [](float size) {
+        mmo_params p{};
+        p.voxel_size = size, p.minimum_points_clearance = 0.2f, p.sigma_dist = 0.5, p.max_corr_distance = 1.0, p.decimation = 10;
+        return p;
+    };
+    CObservation2DRangeScan scan2D;
+    make_scan2d(scan2D);
+    {   // tests/test-mola_metric_maps_hashedvoxels.cpp:44-117
+        mg::HashedVoxelPointCloud map(0.2f);
+        CHECK(map.insertObservation(scan2D));
+        size_t nPts = 0;
+        map.visitAllPoints([&nPts](const TPoint3Df&) { nPts++; });
+        const mmo_params prm = P(0.2f);
+        void*            o   = O.create(0, &prm);
+        if (O.ref_metric_map)
+        {
+            CHECK(static_cast<mrpt::maps::CMetricMap*>(O.ref_metric_map(o))->insertObservation(scan2D));
+            CHECK(nPts == O.num_points(o));
+            check_same_contents(map, O, o);
+        }
+        CHECK(nPts > 300 && nPts == scan2D.buildAuxPointsMap<mrpt::maps::CPointsMap>()->size());
+        mrpt::maps::CSimplePointsMap refPts, queryPts;
+        map.visitAllPoints([&](const TPoint3Df& pt) { refPts.insertPoint(pt); });
+        queryPts.insertObservation(scan2D, mrpt::poses::CPose3D::FromXYZYawPitchRoll(-0.05, -0.01, -0.01, 0, 0, 0));
+        CHECK(queryPts.size() == nPts);
+        const size_t knn = 2;
+        size_t       compared = 0;
+        for (size_t i = 0; i < queryPts.size(); i++)
+        {
+            mrpt::math::TPoint3D qd;
+            queryPts.getPoint(i, qd);
+            const TPoint3Df        query((float)qd.x, (float)qd.y, (float)qd.z);
+            std::vector<TPoint3Df> results, gt_results;
+            std::vector<float>     dists_sqr, gt_dists_sqr;
+            std::vector<uint64_t>  IDs, gt_IDs;
+            map.nn_multiple_search(query, knn, results, dists_sqr, IDs);
+            refPts.nn_multiple_search(query, knn, gt_results, gt_dists_sqr, gt_IDs);
+            CHECK(results.size() == knn);
+            for (size_t k = 0; k < results.size(); k++, compared++)
+            {
+                CHECK(std::fabs(results[k].x - gt_results[k].x) < 1e-3f && std::fabs(results[k].y - gt_results[k].y) < 1e-3f &&
+                      std::fabs(results[k].z - gt_results[k].z) < 1e-3f && std::fabs(dists_sqr[k] - gt_dists_sqr[k]) < 1e-3f);
+            }
+        }
+        CHECK(compared == 2 * nPts);
+        O.destroy(o);
+    }
+    {   // tests/test-sparsevoxelpointcloud.cpp:44-93
+        static_assert(mg::SparseVoxelPointCloud::HARDLIMIT_MAX_POINTS_PER_VOXEL == 16, "the numbers of this test depend on it");
+        mg::SparseVoxelPointCloud map(0.2f);
+        CHECK(map.isEmpty());
+        CHECK(map.insertObservation(scan2D));
+        size_t nPts = 0;
+        map.visitAllPoints([&nPts](const TPoint3Df&) { nPts++; });
+        CHECK(nPts == map.numPoints() && nPts > 300);
+        if (O.ref_metric_map)
+        {
+            const mmo_params prm = P(0.2f);
+            void*            o   = O.create(1, &prm);
+            CHECK(static_cast<mrpt::maps::CMetricMap*>(O.ref_metric_map(o))->insertObservation(scan2D));
+            CHECK(nPts == O.num_points(o) && map.numVoxels() == O.num_voxels(o));
+            check_same_contents(map, O, o);
+            O.destroy(o);
+        }
+    }
+    {   // tests/test-serialization.cpp:35-51 at run time: copies are deep, moves leave a destructible object
+        mg::SparseTreesPointCloud a(5.0f);
+        CHECK(a.insertObservation(scan2D));
+        mg::SparseTreesPointCloud b(a), c(1.0f);
+        c = a;
+        mg::SparseTreesPointCloud d(std::move(a));
+        CHECK(b.numPoints() == d.numPoints() && c.numPoints() == d.numPoints() && d.numPoints() > 0);
+        b.clear();
+        CHECK(b.isEmpty() && !c.isEmpty() && !d.isEmpty());
+        c = std::move(d);
+        CHECK(!c.isEmpty());
+    }
+}
+
+// Const queries from several host threads on ONE map (SURVEY 5 / 8(b) "Threading"; the reference's Hashed queries are
+// read-only and SparseTrees guards its cache with a shared_mutex, SparseTreesPointCloud.h:164-209,449).
+static void run_threads(const Case& c)
+{
+    std::printf("threads %s\n", c.cls);
+    auto  mapPtr = create_from_definition(c);
+    auto* m      = dynamic_cast<mg::GpuPointMapBase*>(mapPtr.get());
+    mrpt::obs::CObservationPointCloud obs;
+    obs.pointcloud = make_scan(30000);
+    CHECK(mapPtr->insertObservation(obs, mrpt::poses::CPose3D::FromXYZYawPitchRoll(1.0, 0.5, 1.7, 0.05, 0.0, 0.01)));
+    const size_t       nq = 20000;
+    std::vector<float> qx(nq), qy(nq), qz(nq);
+    for (size_t i = 0; i < nq; i++) qx[i] = -14.f + 30.f * frand(), qy[i] = -6.f + 12.f * frand(), qz[i] = 4.f * frand();
+    const int T = 8;
+    mg::NNBatchResult s1, sr;
+    if (c.kind != 1) m->nn_single_search_batch(qx.data(), qy.data(), qz.data(), nq, s1);
+    m->nn_radius_search_batch(qx.data(), qy.data(), qz.data(), nq, 0.6f * 0.6f, 4, sr);
+    std::vector<int>         bad(T, 0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < T; t++)
+        th.emplace_back([&, t] {
+            try
+            {
+                for (int rep = 0; rep < 6; rep++)
+                {
+                    // every thread asks for its own slice, so results that leak between threads show up as mismatches
+                    const size_t a = nq * t / T / 2, n = nq / 2;
+                    mg::NNBatchResult r;
+                    if (c.kind != 1)
+                    {
+                        m->nn_single_search_batch(qx.data() + a, qy.data() + a, qz.data() + a, n, r);
+                        for (size_t i = 0; i < n; i++)
+                            if (r.found[i] != s1.found[a + i] || (r.found[i] && (r.ids[i] != s1.ids[a + i] || std::memcmp(&r.dist_sqr[i], &s1.dist_sqr[a + i], 4))))
+                                bad[t]++;
+                    }
+                    mg::NNBatchResult q;
+                    m->nn_radius_search_batch(qx.data() + a, qy.data() + a, qz.data() + a, n, 0.6f * 0.6f, 4, q);
+                    for (size_t i = 0; i < n; i++)
+                    {
+                        const size_t k = q.offsets[i + 1] - q.offsets[i], k0 = sr.offsets[a + i + 1] - sr.offsets[a + i];
+                        if (k != k0 || (k && (std::memcmp(&q.ids[q.offsets[i]], &sr.ids[sr.offsets[a + i]], 8 * k) ||
+                                              std::memcmp(&q.dist_sqr[q.offsets[i]], &sr.dist_sqr[sr.offsets[a + i]], 4 * k))))
+                            bad[t]++;
+                    }
+                }
+            }
+            catch (const std::exception& e)
+            {
+                std::printf("  thread %d: %s\n", t, e.what());
+                bad[t] = -1;
+            }
+        });
+    for (auto& x : th) x.join();
+    for (int t = 0; t < T; t++) CHECK(bad[t] == 0);
+}
+
 int main(int argc, char** argv)
 {
     if (argc < 2)
@@ -479,6 +780,9 @@ int main(int argc, char** argv)
     try
     {
         for (const Case& c : cases) run_case(O, c);
+        for (const Case& c : cases) run_observations(O, c);
+        replay_reference_tests(O);
+        for (int k : {0, 2, 4}) run_threads(cases[k]);
     }
     catch (const std::exception& e)
     {
@@ -486,6 +790,7 @@ int main(int argc, char** argv)
         return 1;
     }
     std::printf("archives cross-checked with the reference classes: %d cases\n", g_archive_cross_checks);
+    std::printf("observation-class calls compared with the reference classes: %d\n", g_observation_checks);
     std::printf(g_fail ? "%d CHECKS FAILED\n" : "ALL OK\n", g_fail);
     return g_fail ? 1 : 0;
 }
