@@ -27,11 +27,31 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+WORKLOAD = "C2: 10M-pt HashedVoxelPointCloud (voxel 0.5 m), batched nn_single_search of 1M points per step per GPU"
 VOXEL = 0.5
 MAP_POINTS = 10_000_000
 N_QUERIES = 1_000_000
 SPACING = 5.0          # metres between map scans
 MAX_SCANS = 900
+
+
+def make_config(map_points, map_voxels, map_scans, queries):
+    """The `config` object, identical in both arms (ours and --impl reference) for the same workload."""
+    return {"workload": WORKLOAD, "map_points": map_points, "map_voxels": map_voxels, "map_scans": map_scans,
+            "queries_per_step_per_gpu": queries,
+            "l2": "GPU arm: L2 flushed between steps (256 MiB write); CPU arm: the 10M-point map (>1 GB of buckets) exceeds the LLC"}
+
+
+def source_stamp():
+    """Hash of the CUDA sources and the C-ABI header: profiles/traffic.json carries the stamp of the tree its ncu capture
+    ran on (tools/ncu_summary.py), and its counters are quoted only when that stamp is this tree's."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "mola_b200", "csrc", "*")) + glob.glob(os.path.join(ROOT, "include", "mola_b200", "*.h"))):
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
 
 
 def compose_host(pose12, xs, ys, zs):
@@ -174,7 +194,7 @@ def run_reference(args, rank, world):
     nscans, n_in = map_scans(args.map_points, om.num_points, ins, log)
     q = query_batch(nscans)
     threads = cpu_threads()
-    sample = min(N_QUERIES, args.cpu_sample)
+    sample = N_QUERIES if args.cpu_sample <= 0 else min(N_QUERIES, args.cpu_sample)  # default: the full 1M-query step
     for _ in range(args.warmup):
         om.nn_single(q[0][:sample], q[1][:sample], q[2][:sample], nthreads=threads)
     t = time.perf_counter()
@@ -186,10 +206,9 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": "nn_single_search queries/s", "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C2: 10M-pt HashedVoxelPointCloud (voxel 0.5 m), batched nn_single_search", "map_points": int(om.num_points()),
-                       "map_voxels": int(om.num_voxels()), "queries_per_step": sample, "map_scans": nscans},
+            "config": make_config(int(om.num_points()), int(om.num_voxels()), nscans, sample),
             "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": threads, "kind": kind,
-                             "sample": f"{sample} of the 1M queries per step, {threads} threads; 1 thread: {qps1:.0f} q/s",
+                             "sample": f"all {sample} queries of the step, {threads} threads (std::thread shards of the const batch); 1 thread on the first 100k: {qps1:.0f} q/s",
                              "value_1thread": qps1, "insert_mpts_s_1thread": n_in / ins_t[0] / 1e6},
             "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "setup_s": time.perf_counter() - t0}
@@ -293,6 +312,14 @@ def run_gpu(args, rank, world, local_rank):
     log = (lambda s: print(s, file=sys.stderr, flush=True)) if (args.verbose and rank == 0) else None
     lib = capi.lib()
     t_setup = time.perf_counter()
+    # process warm-up, untimed: the first launch of every kernel loads its module and the first pool allocation creates the
+    # pool (130 ms on a fresh process, tools/build_trace.py); these are start-up costs of the process, not of a map
+    from mola_b200 import synth as _synth
+    _w = HashedVoxelPointCloud(VOXEL, device=local_rank)
+    _s = _synth.lidar_scan("tiny")
+    _w.insertPointCloud(_s[0], _s[1], _s[2], _s[3])
+    _w.nn_single_search_batch(_s[0], _s[1], _s[2])
+    del _w
     gmap = HashedVoxelPointCloud(VOXEL, device=local_rank)
     stream = torch.cuda.current_stream(dev)
     sp = C.c_void_p(stream.cuda_stream)
@@ -327,13 +354,21 @@ def run_gpu(args, rank, world, local_rank):
         dist.broadcast_object_list(obj, src=0)
         comm = Communicator(obj[0], rank, world, local_rank)
         nscans = obj[1]
+        # the first collective on a new communicator pays NCCL's lazy channel set-up (hundreds of ms); the second one is
+        # the transfer itself (the receivers already hold the map then, the bytes still cross NVLink)
         torch.cuda.synchronize()
+        dist.barrier()
+        tb = time.perf_counter()
+        gmap.broadcast(comm, 0)
+        torch.cuda.synchronize()
+        comm_init_s = time.perf_counter() - tb
+        dist.barrier()
         tb = time.perf_counter()
         gmap.broadcast(comm, 0)
         torch.cuda.synchronize()
         bcast_s = time.perf_counter() - tb
     else:
-        bcast_s = 0.0
+        bcast_s, comm_init_s = 0.0, 0.0
     stats = gmap.tableStats()
     batch_insert = bench_batch_insert(args, dev, local_rank, stream) if rank == 0 else None
     scan_insert = bench_scan_insert(gmap, nscans, dev, stream) if rank == 0 else None
@@ -405,6 +440,63 @@ def run_gpu(args, rank, world, local_rank):
     clocks = sampler.stop() if rank == 0 else None
     found_frac = float(d_found.float().mean().item())
 
+    # ---- multi-GPU extras: identical shards (every rank runs rank 0's batch) and strong scaling (ONE ICP iteration: the
+    # N = 1 batch of 1M queries cut into `world` contiguous shards, results gathered on every rank over NCCL) ------------
+    extra = None
+    if world > 1:
+        q0 = query_batch(nscans, 0, world=world)
+        dq0 = [torch.from_numpy(a).to(dev) for a in q0]
+
+        def step_ident():
+            capi.check(lib.mmg_nn_single_batch(gmap._h, fp(dq0[0]), fp(dq0[1]), fp(dq0[2]), C.c_size_t(n), None, vp(d_found), vp(d_xyz), vp(d_d2),
+                                               vp(d_id), capi.MEM_DEVICE, sp))
+        a, b = n * rank // world, n * (rank + 1) // world
+        sh = [t[a:b].contiguous() for t in dq0]
+        ns = b - a
+        res = torch.empty((ns, 8), dtype=torch.float32, device=dev)       # 32 B/query: xyz, d2, id (2 words), found, pad
+        gat = torch.empty((world * ((n + world - 1) // world), 8), dtype=torch.float32, device=dev)
+        s_found = torch.empty(ns, dtype=torch.uint8, device=dev)
+        s_xyz = torch.empty((ns, 3), dtype=torch.float32, device=dev)
+        s_d2 = torch.empty(ns, dtype=torch.float32, device=dev)
+        s_id = torch.empty(ns, dtype=torch.int64, device=dev)
+        pad = (n + world - 1) // world
+
+        def step_strong():
+            capi.check(lib.mmg_nn_single_batch(gmap._h, fp(sh[0]), fp(sh[1]), fp(sh[2]), C.c_size_t(ns), None, vp(s_found), vp(s_xyz), vp(s_d2),
+                                               vp(s_id), capi.MEM_DEVICE, sp))
+            res[:, 0:3] = s_xyz
+            res[:, 3] = s_d2
+            res[:, 4:6] = s_id.view(torch.float32).view(ns, 2)
+            res[:, 6] = s_found.to(torch.float32)
+            buf = res if ns == pad else torch.cat([res, res.new_zeros((pad - ns, 8))])
+            dist.all_gather_into_tensor(gat, buf)
+
+        def timed(fn):
+            for _ in range(3):
+                flush.zero_()
+                fn()
+            barrier()
+            ev = []
+            for _ in range(args.steps):
+                flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                fn()
+                e1.record(stream)
+                ev.append((e0, e1))
+            barrier()
+            t = torch.tensor([sum(x.elapsed_time(y) for x, y in ev) / args.steps], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t[0])
+        ident_ms = timed(step_ident)
+        strong_ms = timed(step_strong)
+        extra = {"weak_identical_shards": {"ms_per_step": ident_ms, "value": n * world / (ident_ms * 1e-3), "unit": "queries/s",
+                                           "note": "every rank runs rank 0's 1M-query batch on its replica: isolates contention from workload differences"},
+                 "strong": {"ms_per_iteration": strong_ms, "queries": n, "value": n / (strong_ms * 1e-3), "unit": "queries/s",
+                            "gathered_bytes_per_rank": int(gat.numel() * 4),
+                            "note": "one ICP iteration: the N=1 batch split into contiguous shards, 32 B/query of results all-gathered over NCCL; "
+                                    "time = max over ranks, CUDA events around kernel + pack + all_gather"}}
+
     t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     per_rank = [dev_ms / args.steps]
     if world > 1:
@@ -429,42 +521,103 @@ def run_gpu(args, rank, world, local_rank):
     if batch_insert:
         batch_insert["frac_of_hbm_peak"] = batch_insert["achieved_gbs"] / peak
         batch_insert["reobserve"]["frac_of_hbm_peak"] = batch_insert["reobserve"]["achieved_gbs"] / peak
-    achieved = bytes_per_q * n / (dev_ms / args.steps * 1e-3) / 1e9
-    traffic, ncu_note = None, None
+    step_s = dev_ms / args.steps * 1e-3
+    # What bounds the step. The SURVEY 8(d) figure (361 + 12 P-bar bytes per query) counts every stencil probe and every
+    # candidate point as memory traffic; exact pruning and L1/L2 reuse remove nearly all of it, so it is kept as a labelled
+    # extra and NOT used as the roofline. `achieved` = the bytes a step cannot avoid moving (12 B query in + 25 B result out
+    # per query) over the step time; `traffic` = DRAM bytes per step measured by ncu on this very source tree (else null).
+    # The real limiter is instruction issue: `issue` gives warp instructions per step (ncu) over the issue slots of the step.
+    compulsory = 37.0 * n
+    achieved = compulsory / step_s / 1e9
+    roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "kernel": "one step = k_nn_own + k_nn_tasks + k_nn_finish (mmg_nn_single_batch, device pointers)",
+            "algorithmic_bytes_per_query": 37.0, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+            "limiter": "instruction issue + L2 latency, not DRAM bandwidth (see `issue`)",
+            "survey_8d_formula": {"bytes_per_query": bytes_per_q, "mean_stencil_points": pbar.value, "gbs": bytes_per_q * n / step_s / 1e9,
+                                  "x_of_hbm_peak": bytes_per_q * n / step_s / 1e9 / peak,
+                                  "note": "361 + 12*P-bar; > 1 x peak means these bytes never reach DRAM (pruning + L1/L2), it is not a roofline"}}
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic, ncu_note = tj.get("k_nn_single_dram_bytes_per_launch"), tj.get("k_nn_single_ncu")
-    except Exception:
-        pass
+        lab = tj.get("labels", {}).get("nn_single_step")
+        if tj.get("source_stamp") != source_stamp():
+            roof["ncu"] = f"profiles/traffic.json was captured on another source tree (stamp {tj.get('source_stamp')}): not quoted"
+        elif lab:
+            tot = lab["total"]
+            traffic = tot["dram_bytes_read"] + tot["dram_bytes_write"]
+            sm_hz = 1e6 * float((clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0)
+            slots = step_s * 148 * 4 * sm_hz
+            roof["traffic"] = traffic
+            roof["dram_gbs_actual"] = traffic / step_s / 1e9
+            roof["dram_frac_of_peak"] = traffic / step_s / 1e9 / peak
+            roof["issue"] = {"warp_instructions_per_step": tot["warp_instructions"], "issue_slots_per_step": slots,
+                             "frac_of_issue_peak": tot["warp_instructions"] / slots, "sm_mhz": sm_hz / 1e6,
+                             "note": "ncu smsp__inst_executed.sum of the step's kernels / (step time x 148 SMs x 4 schedulers x SM clock)"}
+            roof["ncu"] = {"source": lab.get("source"), "kernels": lab["kernels"]}
+    except Exception as e:  # no capture for this tree yet
+        roof["ncu"] = f"no usable profiles/traffic.json ({type(e).__name__})"
     line = {"metric": "nn_single_search queries/s", "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C2: 10M-pt HashedVoxelPointCloud (voxel 0.5 m), batched nn_single_search of 1M points per step per GPU",
-                       "map_points": int(stats["points"]), "map_voxels": int(stats["live_voxels"]), "map_scans": nscans,
-                       "queries_per_step_per_gpu": n, "l2": "flushed between steps (256 MiB write)", "map_hbm_bytes": int(stats["hbm_bytes"]),
-                       "parallelism": f"map replicated by NCCL broadcast, queries sharded x{world} (scan points x ICP pose guesses: one guess per rank)", "rank0_cpu_binding": numa},
+            "config": make_config(int(stats["points"]), int(stats["live_voxels"]), nscans, n),
+            "sharding": {"parallelism": f"map replicated by NCCL broadcast, queries sharded x{world} (scan points x ICP pose guesses: one guess per rank)",
+                         "rank0_cpu_binding": numa, "map_hbm_bytes": int(stats["hbm_bytes"])},
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": 12 * n, "d2h_bytes_per_step": 25 * n},
             "gpu_launches": int(launches), "ms_per_step_by_rank": per_rank,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "kernel": "k_nn_single_pruned<HashedTraits>", "algorithmic_bytes_per_query": bytes_per_q, "mean_stencil_points": pbar.value,
-                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
-                         "dram_gbs_actual": (traffic * 1e-9 / (dev_ms / args.steps * 1e-3)) if traffic else None,
-                         "note": "frac > 1: the algorithmic bytes of SURVEY 8(d) never reach DRAM (exact pruning + L2 reuse); see ncu", "ncu": ncu_note},
+            "roofline": roof,
             "clocks": clocks, "found_frac": found_frac, "wall_ms_per_step_incl_flush": 1e3 * wall_s / args.steps,
             "insert": {"mpts_s": n_in / (ins_ms[0] * 1e-3) / 1e6 if ins_ms[0] else None, "points_in": n_in, "scans": nscans,
                        "note": "the map build itself: per-scan calls interleaved with scan synthesis (and the CPU twin at N=1), summed CUDA-event time; "
                                "see insert_per_scan for back-to-back calls"},
             "insert_per_scan": scan_insert, "insert_batched": batch_insert,
             "table": {k: stats[k] for k in ("capacity", "load_factor", "mean_probe", "max_probe")},
-            "bcast_s": bcast_s, "setup_s": time.perf_counter() - t_setup}
+            "bcast_s": bcast_s, "comm_init_s": comm_init_s, "multi_gpu": extra, "setup_s": time.perf_counter() - t_setup}
     if om is not None:
         threads = cpu_threads()
-        sample = min(n, args.cpu_sample)
+        sample = min(n, args.cpu_sample if args.cpu_sample > 0 else 200_000)
         qps_mt, _ = time_cpu_queries(om, q, sample, threads, repeats=2)
         qps_1, _ = time_cpu_queries(om, q, min(sample, 100_000), 1, repeats=2)
         line["cpu_baseline"] = {"value": qps_mt, "unit": "queries/s", "cores": threads, "kind": cpu_kind,
                                 "sample": f"first {sample} of the 1M queries on the same 10M-pt map, {threads} threads (1 thread: {qps_1:.0f} q/s)",
                                 "value_1thread": qps_1, "insert_mpts_s_1thread": n_in / cpu_ins_s[0] / 1e6 if cpu_ins_s[0] else None}
+    emit(json.dumps(line))
+
+
+def run_config(args, rank, world, local_rank):
+    """--config c4 | c5: the multi-GPU BASELINE configurations as bench lines (the legs themselves live in
+    tests/bench_configs.py because each also checks the CUDA path against the CPU reference while timing it).
+      c4: 50M-pt SparseTreesPointCloud, nn_radius_search sweep r = 0.2 .. 2 m x maxPoints 0 / 16, queries sharded over the ranks
+      c5: 64 OS1-128 scans inserted in one call, map replicated over NCCL, every scan queried on rank scan % N"""
+    import argparse as ap
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import bench_configs as bc
+    ctx = bc.Ctx()
+    ctx.args = ap.Namespace(c3_scans=40, c4_points=args.c4_points, c4_max_scans=6000, c4_spacing=2.0, c4_queries=200_000,
+                            c4_cpu_scans=0 if args.no_cpu else 6, c4_cpu_queries=5000, c5_scans=args.insert_scans or 64,
+                            c5_check=0 if args.no_cpu else 1)
+    ctx.rank, ctx.world, ctx.local_rank = rank, world, local_rank
+    torch.cuda.set_device(local_rank)
+    ctx.dev = torch.device("cuda", local_rank)
+    ctx.stream = torch.cuda.current_stream(ctx.dev)
+    t0 = time.perf_counter()
+    out = (bc.run_c4 if args.config == "c4" else bc.run_c5)(ctx)
+    if rank != 0 or out is None:
+        return
+    base = {"n_gpus": world, "steps": 2, "warmup": 1, "higher_is_better": True, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "gpu_launches": int(__import__("mola_b200").capi.lib().mmg_kernel_launch_count()), "wall_s": time.perf_counter() - t0}
+    if args.config == "c4":
+        head = [x for x in out["sweep"] if x["r"] == 2.0 and x["maxPoints"] == 0][0]
+        line = dict(base, metric="nn_radius_search queries/s (r = 2 m, maxPoints = 0)", value=head["qps"], unit="queries/s", ms_per_step=head["ms"],
+                    scaling="strong", config={"workload": "C4: " + out["workload"], "stored_points": out["stored_points"], "blocks": out["blocks"],
+                                              "map_scans": out["scans"]},
+                    result_stream_gbs=24.0 * head["hits"] / (head["ms"] * 1e-3) / 1e9, sweep=out["sweep"],
+                    insert={"mpts_s": out["insert_mpts_s"], "points_in": out["points_in"], "s": out["insert_s"]}, bcast_s=out["bcast_s"],
+                    nn_single_qps=out["nn_single_qps"], cpu_baseline=out.get("cpu"))
+    else:
+        line = dict(base, metric="nn_single_search queries/s (64 OS1-128 scans against the replicated map)", value=out["query_qps"], unit="queries/s",
+                    ms_per_step=out["query_ms"], scaling="strong", config={"workload": "C5: " + out["workload"], "points": out["points"],
+                                                                              "stored_points": out["stored_points"], "voxels": out["voxels"]},
+                    insert={"mpts_s": out["insert_mpts_s"], "ms": out["insert_ms"]}, bcast_ms=out["bcast_ms"], parity_bit_exact_sample=out["parity_bit_exact_sample"])
     emit(json.dumps(line))
 
 
@@ -496,11 +649,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--map-points", type=int, default=MAP_POINTS)
-    ap.add_argument("--cpu-sample", type=int, default=200_000)
+    ap.add_argument("--cpu-sample", type=int, default=0, help="--impl reference: queries per step (0 = the full 1M-query step); "
+                    "ours: size of the cpu_baseline sample (0 = 200k)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--insert-scans", type=int, default=64, help="OS1-128 scans in the batched-insert measurement (0 = skip)")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--only", default="", choices=["", "insert_batched"], help="profiling aid: run one leg only")
+    ap.add_argument("--config", default="c2", choices=["c2", "c4", "c5"], help="BASELINE.json configuration: c2 = the headline (default); "
+                    "c4 = 50M-pt SparseTrees radius sweep, queries sharded; c5 = 64 OS1-128 scans inserted, replicated, queried")
+    ap.add_argument("--c4-points", type=int, default=50_000_000)
     args = ap.parse_args()
     quiet_stdout()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -517,7 +674,10 @@ def main():
             os.environ["NCCL_DEBUG"] = "WARN"  # keeps NCCL's version banner out of stdout: the JSON line stays alone there
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
-        run_gpu(args, rank, world, local_rank)
+        if args.config != "c2":
+            run_config(args, rank, world, local_rank)
+        else:
+            run_gpu(args, rank, world, local_rank)
     finally:
         if world > 1:
             import torch.distributed as dist

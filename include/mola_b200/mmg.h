@@ -168,6 +168,18 @@ int mmg_match_batch(const mmg_map* m, const float* xs, const float* ys, const fl
                     uint32_t* out_local_idx, float* out_xyz /*map point*/, float* out_d2, uint64_t* out_id,
                     int mem, void* stream);
 
+/* Point-to-plane pairing against a SparseVoxelPointCloud (extension, SURVEY N4: the reference has the per-voxel running
+ * mean, SparseVoxelPointCloud.cpp:193-204, and no covariance; mp2p_icp's plane matchers are outside the reference tree).
+ * Each local point, composed with pose12, is paired with the voxel it falls into when that voxel stores >= min_points
+ * (>= 3) points and the point lies within max_dist_sqr of the voxel's running mean. Per pairing, compacted in local-point
+ * order: local index, running mean (3), unit normal of the plane fitted to the voxel's stored points (3; eigenvector of
+ * the smallest eigenvalue of their covariance, largest component positive), signed point-to-plane distance, and the two
+ * smallest eigenvalues (2) for planarity thresholds. Arrays are sized for n pairings; *out_count (host) = pairings written. */
+int mmg_match_planes_batch(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n,
+                           const double* pose12, float max_dist_sqr, uint32_t min_points, uint64_t* out_count,
+                           uint32_t* out_local_idx, float* out_mean, float* out_normal, float* out_plane_dist,
+                           float* out_eig, int mem, void* stream);
+
 /* log-likelihood of a scan, see reference :509-546. */
 int mmg_likelihood(const mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n,
                    const double* pose12, double* out_loglik, int mem, void* stream);

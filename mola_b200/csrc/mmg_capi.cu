@@ -19,7 +19,7 @@
 namespace mmg
 {
 std::atomic<unsigned long long> g_launches{0};
-int                       g_tune[T_COUNT] = {0, 8, 4096, 1};
+int                       g_tune[T_COUNT] = {0, 16, 4096, 1, 1 << 26, 0x7FFFFFFF, 6, 1 << 17};
 static thread_local char  g_err[512] = "";
 void set_error(const char* fmt, ...)
 {
@@ -42,6 +42,7 @@ PoseD mmg::make_pose(const double* pose12)
 
 namespace mmg
 {
+static thread_local bool          t_in_insert = false;  // set by the insert entry points: they settle lazily themselves
 static thread_local ScratchScope* t_scope = nullptr;
 // per-thread hit buffers of the radius searches (S_RHITS, S_RHITS2): grow-only, released when the thread ends
 struct TlsRad
@@ -158,7 +159,10 @@ static int init_counters(mmg_map* m, bool keep_bbox)
     return MMG_OK;
 }
 
-int mmg::alloc_table(mmg_map* m, u64 cap)
+// Table and row store are plain cudaMalloc blocks. (Tried in round 2: the stream-ordered pool, cudaMallocAsync /
+// cudaFreeAsync. Growing the pool by a few hundred MB cost 10-14 ms per growth on the B200 box against 1-2 ms for
+// cudaMalloc, tools/build_trace.py; growths are rare, so the stream synchronisation cudaMalloc / cudaFree imply is cheap.)
+int mmg::alloc_table(mmg_map* m, u64 cap, cudaStream_t st)
 {
     Entry* t = nullptr;
     if (cap > (1ull << 32))
@@ -172,23 +176,26 @@ int mmg::alloc_table(mmg_map* m, u64 cap)
         cudaGetLastError();
         return MMG_ERR_OUT_OF_MEM;
     }
-    MMG_CUDA(cudaMemset(t, 0xFF, cap * sizeof(Entry)));
-    if (m->dev.table) cudaFree(m->dev.table);
+    MMG_CUDA(cudaMemsetAsync(t, 0xFF, cap * sizeof(Entry), st));
+    if (m->dev.table)
+    {
+        MMG_CUDA(cudaStreamSynchronize(st));
+        cudaFree(m->dev.table);
+    }
     m->dev.table = t;
     m->dev.mask  = cap - 1;
     m->cap       = cap;
     return MMG_OK;
 }
 
-// Makes room for `entries` keys at load factor <= 0.5 (the reference's robin_map also keeps
-// max load 0.5); rebuilds the table from the live rows when it grows.
+// Makes room for `entries` keys at load factor <= 0.5 (the reference's robin_map also keeps max load 0.5); rebuilds the
+// table from the live rows when it grows (exact counters needed: the callers settle() first).
 static int ensure_table(mmg_map* m, u64 entries, cudaStream_t st)
 {
     u64 cap = 1024;
     while (cap < 2 * entries) cap <<= 1;
     if (cap <= m->cap) return MMG_OK;
-    MMG_CUDA(cudaStreamSynchronize(st));
-    int rc = alloc_table(m, cap);
+    int rc = alloc_table(m, cap, st);
     if (rc) return rc;
     if (m->h_nvox_hi) MMG_LAUNCH(k_rebuild_table, (m->h_nvox_hi + 255) / 256, 256, 0, st, m->dev, m->h_nvox_hi);
     return MMG_OK;
@@ -206,8 +213,11 @@ static int grow_array(T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
     }
     if (oldn) MMG_CUDA(cudaMemcpyAsync(q, *p, oldn * sizeof(T), cudaMemcpyDeviceToDevice, st));
     MMG_CUDA(cudaMemsetAsync(q + oldn, fill_byte, (newn - oldn) * sizeof(T), st));
-    MMG_CUDA(cudaStreamSynchronize(st));
-    if (*p) cudaFree(*p);
+    if (*p)
+    {
+        MMG_CUDA(cudaStreamSynchronize(st));
+        cudaFree(*p);
+    }
     *p = q;
     return MMG_OK;
 }
@@ -215,7 +225,10 @@ static int grow_array(T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
 int mmg::ensure_rows(mmg_map* m, u64 rows, cudaStream_t st)
 {
     if (rows <= m->rowcap) return MMG_OK;
-    const u64 newcap = std::max<u64>(rows + rows / 2, 4096);
+    // geometric growth from a floor of 256k rows (136 MB for a Hashed map, 0.08 % of the HBM): a KITTI-scale map (389k
+    // voxels) grows its row store once or twice in its life, and the copies of all growths together move less than twice
+    // the final size
+    const u64 newcap = std::max<u64>(2 * rows, (u64)1 << 18);
     const u64 cap_pts = (u64)m->row_points();
     int       rc;
     if ((rc = grow_array(&m->dev.pts, m->rowcap * cap_pts, newcap * cap_pts, 0, st))) return rc;
@@ -225,6 +238,22 @@ int mmg::ensure_rows(mmg_map* m, u64 rows, cudaStream_t st)
     if ((rc = grow_array(&m->dev.fill, m->rowcap, newcap, 0, st))) return rc;
     if (m->kind == MMG_SPARSE_VOXEL && (rc = grow_array(&m->dev.mean, m->rowcap, newcap, 0, st))) return rc;
     m->rowcap = newcap;
+    return MMG_OK;
+}
+
+int mmg::settle(const mmg_map* cm)
+{
+    mmg_map* m = const_cast<mmg_map*>(cm);
+    if (!m->ctr_pending.load(std::memory_order_acquire)) return MMG_OK;
+    std::lock_guard<std::mutex> lk(m->ctr_mtx);
+    if (!m->ctr_pending.load(std::memory_order_relaxed)) return MMG_OK;
+    MMG_CUDA(cudaEventSynchronize(m->ev_ctr));
+    const Counters c  = *m->h_ctr;  // written by the last block of the last k_insert_commit
+    m->h_nvox_hi      = c.nvox_hi;
+    m->h_free_n       = c.free_n;
+    m->deferred_oob += c.oob;
+    m->pending_points = 0;
+    m->ctr_pending.store(false, std::memory_order_release);
     return MMG_OK;
 }
 
@@ -284,7 +313,8 @@ static int evict_far(mmg_map* m, const double* pose12, cudaStream_t st)
 // The batch is cut into chunks so that the worst case "every point opens a new voxel" bounds the
 // table and row growth per chunk; one 64-byte counter read-back per chunk is the only sync.
 template <class Tr>
-static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const float* dz, size_t n, const ScanSet& S0, cudaStream_t st, u32* oob_out)
+static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const float* dz, size_t n, const ScanSet& S0, cudaStream_t st, u32* oob_out,
+                         bool async)
 {
     const mmg_params& P        = m->prm;
     const u32         hard     = (u32)Tr::CAP;
@@ -292,23 +322,39 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
     const u32         eff      = uncapped ? hard : P.max_points_per_voxel;
     MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->oob, 0, 2 * sizeof(u32), st));  // oob, nseg: they run on from chunk to chunk
     static_assert(offsetof(Counters, nseg) == offsetof(Counters, oob) + sizeof(u32), "oob and nseg are cleared by one memset");
-    Counters c;
-    memset(&c, 0, sizeof(c));
-    u32 seg_base = 0;
+    u32 seg_base = 0, oob = 0;
     for (size_t a = 0; a < n;)
     {
-        const u64    live = m->h_nvox_hi - m->h_free_n;
+        int rc;
+        // rows / voxels in use, exact or (asynchronous batches in flight) bounded from above
+        u64 hi_ub   = (u64)m->h_nvox_hi + m->pending_points;
+        u64 live_ub = hi_ub - m->h_free_n;
         // chunk: at least 1M points, up to 8M for big batches (worst case "every point opens a voxel": 4.3 GB of row
         // headroom, 2 % of a B200's HBM), more when the map is already large or was reserved (mmg_reserve) for more;
         // a short tail is taken along instead of paying another launch pair + counter read-back for it
-        const u64    room_rows = m->rowcap > m->h_nvox_hi ? m->rowcap - m->h_nvox_hi : 0;
-        const u64    room_tab  = m->cap / 2 > live ? m->cap / 2 - live : 0;
-        u64          want      = std::max<u64>({(u64)1 << 20, 4 * live, std::min<u64>(n - a, (u64)8 << 20), std::min(room_rows, room_tab)});
+        const u64 room_rows = m->rowcap > hi_ub ? m->rowcap - hi_ub : 0;
+        const u64 room_tab  = m->cap / 2 > live_ub ? m->cap / 2 - live_ub : 0;
+        u64       want      = std::max<u64>({(u64)1 << 20, 4 * live_ub, std::min<u64>(n - a, (u64)8 << 20), std::min(room_rows, room_tab)});
         if (n - a > want && n - a - want < want / 4) want = n - a;
-        const size_t k = std::min<size_t>({n - a, (size_t)RANK_MAX_CHUNK, (size_t)want});
-        int          rc;
-        if ((rc = ensure_table(m, live + k, st))) return rc;
-        if ((rc = ensure_rows(m, (u64)m->h_nvox_hi + k, st))) return rc;
+        size_t k = std::min<size_t>({n - a, (size_t)RANK_MAX_CHUNK, (size_t)want});
+        if (m->ctr_pending.load(std::memory_order_acquire) && (live_ub + k > m->cap / 2 || hi_ub + k > m->rowcap))
+        {   // the bound no longer fits: get the exact counters before anything grows
+            if ((rc = settle(m))) return rc;
+            hi_ub = m->h_nvox_hi, live_ub = hi_ub - m->h_free_n;
+        }
+        if (hi_ub + k > m->rowcap)
+        {   // the row store must grow for the worst case "every point opens a voxel": keep that within half of the free memory
+            size_t free_b = 0, total_b = 0;
+            if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess)
+            {
+                const u64 row_bytes = (u64)m->row_points() * sizeof(float4) + 40;
+                const u64 fit       = free_b / 2 / (2 * row_bytes);  // ensure_rows doubles, and the old array lives until the copy is done
+                if (fit > hi_ub) k = std::min<size_t>(k, std::max<u64>(fit - hi_ub, (u64)1 << 16));
+            }
+            cudaGetLastError();
+        }
+        if ((rc = ensure_table(m, live_ub + k, st))) return rc;
+        if ((rc = ensure_rows(m, hi_ub + k, st))) return rc;
         u32* touched = (u32*)m->scratch_get(S_SEG, k * sizeof(u32));
         if (!touched) return MMG_ERR_OUT_OF_MEM;
         ScanSet S = S0;
@@ -323,15 +369,20 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
         MMG_LAUNCH((k_insert_commit<Tr>), fb, 256, 0, st, m->dev, touched, dx + a, dy + a, dz + a, (u32)a, S, m->inv, uncapped ? 0 : 1,
                    m->kind == MMG_SPARSE_VOXEL ? 1 : 0, seg_base, m->h_ctr);
         MMG_CUDA(cudaGetLastError());
-        // the commit kernel's last block has mirrored the counters into the pinned block: wait, no copy call
-        MMG_CUDA(cudaStreamSynchronize(st));
-        c        = *m->h_ctr;
-        seg_base = c.nseg;
-        m->h_nvox_hi = c.nvox_hi;
-        m->h_free_n  = c.free_n;
+        // the commit kernel's last block mirrors the counters into the pinned block: an event marks the moment, no copy call
+        MMG_CUDA(cudaEventRecord(m->ev_ctr, st));
+        m->pending_points += k;
+        m->ctr_pending.store(true, std::memory_order_release);
         a += k;
+        if (a < n || !async)
+        {   // the next chunk continues the touched-voxel list: it needs this chunk's counters
+            if ((rc = settle(m))) return rc;
+            seg_base = m->h_ctr->nseg;
+        }
     }
-    *oob_out = c.oob;
+    oob             = m->deferred_oob;  // everything settled so far, earlier asynchronous batches included
+    m->deferred_oob = 0;
+    *oob_out        = oob;
     return MMG_OK;
 }
 
@@ -340,9 +391,10 @@ static int insert_voxel(mmg_map* m, const float* xs, const float* ys, const floa
                         cudaStream_t st)
 {
     const mmg_params& P = m->prm;
-    if (m->kind == MMG_HASHED_VOXEL && has_robot_pose && pose12 && P.remove_voxels_farther_than > 0 && m->h_nvox_hi > 0)
+    if (m->kind == MMG_HASHED_VOXEL && has_robot_pose && pose12 && P.remove_voxels_farther_than > 0)
     {
-        int rc = evict_far(m, pose12, st);
+        int rc = settle(m);  // the eviction sweeps the rows: exact counters first
+        if (!rc && m->h_nvox_hi > 0) rc = evict_far(m, pose12, st);
         if (rc) return rc;
     }
     if (n == 0) return MMG_OK;
@@ -362,15 +414,16 @@ static int insert_voxel(mmg_map* m, const float* xs, const float* ys, const floa
     {
         ScanSet S{nullptr, nullptr, 1, 0.f, make_pose(pose12)};
         u32     oob = 0;
-        if ((rc = insert_ranked<Tr>(m, dx, dy, dz, n, S, st, &oob))) return rc;
+        if ((rc = insert_ranked<Tr>(m, dx, dy, dz, n, S, st, &oob, mem == MMG_MEM_DEVICE))) return rc;
         m->points_dirty = true;
         if (oob)
         {
-            set_error("%u of %zu points have a voxel index outside +-2^20 and were skipped", oob, n);
+            set_error("%u points of this batch (or of earlier asynchronous batches) have a voxel index outside +-2^20 and were skipped", oob);
             return MMG_ERR_OUT_OF_RANGE;
         }
         return MMG_OK;
     }
+    if ((rc = settle(m))) return rc;
     const u64 live = m->h_nvox_hi - m->h_free_n;
     if ((rc = ensure_table(m, live + n, st))) return rc;
 
@@ -404,7 +457,8 @@ static int insert_voxel(mmg_map* m, const float* xs, const float* ys, const floa
     MMG_LAUNCH((k_fold<Tr>), fb, 256, 0, st, m->dev, svid, sidx, segs, (u32)n, gp, m->inv, P.max_points_per_voxel, use_thr ? thr : 0.f, bbox_acc,
                m->kind == MMG_SPARSE_VOXEL ? 1 : 0);
     MMG_CUDA(cudaGetLastError());
-    if (mem == MMG_MEM_HOST) MMG_CUDA(cudaStreamSynchronize(st));
+    // this path keeps no lazy counters: calls that read the map on another stream (mmg_bbox, exports) must find it complete
+    MMG_CUDA(cudaStreamSynchronize(st));
     m->points_dirty = true;
     if (c.oob)
     {
@@ -425,8 +479,9 @@ struct OutBufs
 
 template <class Tr>
 static int launch_nn_single(const mmg_map* m, const float* dx, const float* dy, const float* dz, size_t nq, size_t stride, const PoseD& T, int use_pose,
-                             const QueryOut& o, cudaStream_t st, float bd_init = INFINITY)
+                             const QueryOut& o, cudaStream_t st, float bd_init = INFINITY, const MatchOut* match = nullptr, char* wb_ext = nullptr)
 {
+    // `match` (pipeline only): write compacted pairings through k_nn_finish_match instead of dense results
     // A/B switch for the profiles: MMG_NN_KERNEL = tasks (default) | pruned | grouped | simple, or mmg_set_tuning("nn_kernel", 0..3)
     static const int env_variant = [] {
         const char* e = getenv("MMG_NN_KERNEL");
@@ -437,12 +492,13 @@ static int launch_nn_single(const mmg_map* m, const float* dx, const float* dy, 
     {   // three-kernel pipeline over a global task queue (mmg_query.cuh); its scratch comes from the stream-ordered pool, so
         // concurrent callers on one map never share state
         const size_t c0 = std::min<size_t>(nq, NN_CHUNK);
-        const size_t off_key = 16 * c0, off_q = off_key + 8 * c0, off_cnt = off_q + 104 * c0;
-        char*        wb = nullptr;
-        if (cudaMallocAsync((void**)&wb, off_cnt + 16, st) != cudaSuccess)
+        const size_t off_key = 16 * c0, off_q = off_key + 8 * c0, off_cnt = off_q + 104 * c0, off_status = off_cnt + 32;
+        const size_t tiles0 = (c0 + 255) / 256, wbytes = off_status + (match ? tiles0 * 8 : 0);
+        char*        wb = wb_ext;  // a caller that runs several passes on several streams brings its own work buffers
+        if (!wb && cudaMallocAsync((void**)&wb, wbytes, st) != cudaSuccess)
         {
             cudaGetLastError();
-            set_error("cudaMallocAsync(%zu) failed", off_cnt + 16);
+            set_error("cudaMallocAsync(%zu) failed", wbytes);
             return MMG_ERR_OUT_OF_MEM;
         }
         NNWork W;
@@ -456,10 +512,23 @@ static int launch_nn_single(const mmg_map* m, const float* dx, const float* dy, 
             MMG_LAUNCH((k_nn_own<Tr>), (k + NN_OWN_BLOCK - 1) / NN_OWN_BLOCK, NN_OWN_BLOCK, 0, st, m->dev, dx + a * stride, dy + a * stride, dz + a * stride, k,
                        (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, bd_init, W);
             const unsigned tb = (unsigned)std::min<size_t>(((size_t)k * 26 + 255) / 256, (size_t)m->num_sms * g_tune[T_NN_TASK_BLOCKS]);
-            MMG_LAUNCH((k_nn_tasks<Tr>), tb, 256, 0, st, m->dev, m->inv, m->prm.voxel_size, W);
-            MMG_LAUNCH((k_nn_finish<Tr>), (k + 255) / 256, 256, 0, st, m->dev, k, m->inv, W, oc);
+            switch (g_tune[T_NN_TASK_MINB])
+            {
+                case 8: MMG_LAUNCH((k_nn_tasks<Tr, 8>), tb, 256, 0, st, m->dev, m->inv, m->prm.voxel_size, W); break;
+                case 6: MMG_LAUNCH((k_nn_tasks<Tr, 6>), tb, 256, 0, st, m->dev, m->inv, m->prm.voxel_size, W); break;
+                default: MMG_LAUNCH((k_nn_tasks<Tr, 5>), tb, 256, 0, st, m->dev, m->inv, m->prm.voxel_size, W); break;
+            }
+            if (match)
+            {
+                MatchOut mo = *match;
+                mo.status = (u64*)(wb + off_status), mo.ticket = W.count + 3;  // count[3] is zeroed with the queue tails
+                MMG_CUDA(cudaMemsetAsync(mo.status, 0, ((k + 255) / 256) * 8, st));
+                MMG_LAUNCH((k_nn_finish_match<Tr>), (k + 255) / 256, 256, 0, st, m->dev, k, (u32)a, m->inv, W, mo);
+            }
+            else
+                MMG_LAUNCH((k_nn_finish<Tr>), (k + 255) / 256, 256, 0, st, m->dev, k, m->inv, W, oc);
         }
-        cudaFreeAsync(wb, st);
+        if (!wb_ext) cudaFreeAsync(wb, st);
         return MMG_OK;
     }
     const int variant = kv - 1;
@@ -541,8 +610,52 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
         cudaGetLastError();
         if (all)
         {
-            const int rc = launch_nn_single<Tr>(m, (const float*)dp[0], (const float*)dp[1], (const float*)dp[2], nq, 1, T, pose12 ? 1 : 0,
-                                                QueryOut{(uint8_t*)dp[3], (float*)dp[4], (float*)dp[5], (u64*)dp[6]}, st, bd_init);
+            const float *  hx = (const float*)dp[0], *hy = (const float*)dp[1], *hz = (const float*)dp[2];
+            const QueryOut ho{(uint8_t*)dp[3], (float*)dp[4], (float*)dp[5], (u64*)dp[6]};
+            const size_t   CH = (size_t)std::max(4096, g_tune[T_E2E_CHUNK]);
+            int            rc = MMG_OK;
+            if (nq >= 2 * CH)
+            {   // the pipeline's first stage reads the queries over PCIe and its last one writes the results: chunks alternate
+                // between the caller's stream and an auxiliary one, so the reads of one chunk overlap the writes of another
+                // (both directions of the link busy, as the single-kernel path of round 1 had it)
+                static thread_local struct Aux
+                {
+                    int          dev = -1;
+                    cudaStream_t s   = nullptr;
+                    cudaEvent_t  e0 = nullptr, e1 = nullptr;
+                } aux;
+                if (aux.dev != m->device)
+                {
+                    MMG_CUDA(cudaStreamCreateWithFlags(&aux.s, cudaStreamNonBlocking));
+                    MMG_CUDA(cudaEventCreateWithFlags(&aux.e0, cudaEventDisableTiming));
+                    MMG_CUDA(cudaEventCreateWithFlags(&aux.e1, cudaEventDisableTiming));
+                    aux.dev = m->device;
+                }
+                // one work buffer per stream, both taken from the pool on the caller's stream before the fork and given back
+                // after the join: blocks that move between streams through the pool would chain the streams together
+                const size_t wbytes = 128 * CH + 64;
+                char*        wb2    = nullptr;
+                if (cudaMallocAsync((void**)&wb2, 2 * wbytes, st) != cudaSuccess)
+                {
+                    cudaGetLastError();
+                    set_error("cudaMallocAsync(%zu) failed", 2 * wbytes);
+                    return MMG_ERR_OUT_OF_MEM;
+                }
+                MMG_CUDA(cudaEventRecord(aux.e0, st));
+                MMG_CUDA(cudaStreamWaitEvent(aux.s, aux.e0, 0));
+                int c = 0;
+                for (size_t a = 0; a < nq && !rc; a += CH, c++)
+                {
+                    const size_t k = std::min(CH, nq - a);
+                    rc = launch_nn_single<Tr>(m, hx + a, hy + a, hz + a, k, 1, T, pose12 ? 1 : 0, QueryOut{ho.found + a, ho.xyz + 3 * a, ho.d2 + a, ho.id + a},
+                                              (c & 1) ? aux.s : st, bd_init, nullptr, wb2 + (c & 1) * wbytes);
+                }
+                MMG_CUDA(cudaEventRecord(aux.e1, aux.s));
+                MMG_CUDA(cudaStreamWaitEvent(st, aux.e1, 0));
+                cudaFreeAsync(wb2, st);
+            }
+            else
+                rc = launch_nn_single<Tr>(m, hx, hy, hz, nq, 1, T, pose12 ? 1 : 0, ho, st, bd_init);
             if (rc) return rc;
             MMG_CUDA(cudaGetLastError());
             MMG_CUDA(cudaStreamSynchronize(st));
@@ -667,13 +780,17 @@ static int radius_hashed(mmg_map* m, const float* xs, const float* ys, const flo
 }
 
 // ------------------------------------------------------------------ C ABI
+// every entry point first collects the counters of asynchronous inserts still in flight; the cap-only insert path itself
+// only does so when its upper bounds no longer fit (insert_ranked)
+static inline int settle_unless_insert(const mmg_map* m) { return m->ctr_pending.load(std::memory_order_acquire) && !mmg::t_in_insert ? settle(m) : MMG_OK; }
 #define MMG_CHECK_MAP(m)                          \
     if (!(m))                                     \
     {                                             \
         set_error("null map handle");             \
         return MMG_ERR_INVALID_ARG;               \
     }                                             \
-    MMG_CUDA(cudaSetDevice((m)->device))
+    MMG_CUDA(cudaSetDevice((m)->device));         \
+    if (int rc__ = settle_unless_insert(m)) return rc__
 
 // ------------------------------------------------------------------ matcher
 static __global__ void k_match_threshold(uint8_t* __restrict__ found, const float* __restrict__ d2, u32 n, float max_d2)
@@ -713,6 +830,37 @@ extern "C" int mmg_match_batch(const mmg_map* cm, const float* xs, const float* 
     const float *dx, *dy, *dz;
     int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
     if (rc) return rc;
+    // "d2 < max" as the initial search radius: the largest float below max (nothing when max <= 0)
+    const float bd_thr = std::isinf(max_dist_sqr) && max_dist_sqr > 0 ? INFINITY : std::nextafterf(max_dist_sqr, -INFINITY);
+    static const int env_kernel = [] { const char* e = getenv("MMG_NN_KERNEL"); return e && strcmp(e, "tasks") ? 1 : 0; }();
+    if (m->kind == MMG_HASHED_VOXEL && n >= (size_t)g_tune[T_NN_MIN_PIPE] && g_tune[T_NN_KERNEL] == 0 && !env_kernel)
+    {   // fused: own voxel -> neighbour tasks -> compacted pairings, no dense intermediate (k_nn_finish_match)
+        char* cb = nullptr;
+        if (mem == MMG_MEM_HOST && !(cb = (char*)m->scratch_get(S_MATCH, n * 28 + 64))) return MMG_ERR_OUT_OF_MEM;
+        u32* tot = (u32*)m->scratch_get(S_LIK, 64);
+        if (!tot) return MMG_ERR_OUT_OF_MEM;
+        MMG_CUDA(cudaMemsetAsync(tot, 0, sizeof(u32), st));
+        MatchOut mo{};
+        if (mem == MMG_MEM_HOST) mo.id = (u64*)cb, mo.xyz = (float*)(cb + n * 8), mo.d2 = (float*)(cb + n * 20), mo.idx = (u32*)(cb + n * 24);
+        else mo.id = (u64*)out_id, mo.xyz = out_xyz, mo.d2 = out_d2, mo.idx = out_local_idx;
+        mo.total = tot;
+        rc = launch_nn_single<HashedTraits>(m, dx, dy, dz, n, 1, make_pose(pose12), pose12 ? 1 : 0, QueryOut{}, st, bd_thr, &mo);
+        if (rc) return rc;
+        MMG_CUDA(cudaGetLastError());
+        u32 total = 0;
+        MMG_CUDA(cudaMemcpyAsync(&total, tot, sizeof(u32), cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaStreamSynchronize(st));
+        *out_count = total;
+        if (mem == MMG_MEM_HOST && total)
+        {
+            MMG_CUDA(cudaMemcpyAsync(out_id, mo.id, (size_t)total * 8, cudaMemcpyDeviceToHost, st));
+            MMG_CUDA(cudaMemcpyAsync(out_xyz, mo.xyz, (size_t)total * 12, cudaMemcpyDeviceToHost, st));
+            MMG_CUDA(cudaMemcpyAsync(out_d2, mo.d2, (size_t)total * 4, cudaMemcpyDeviceToHost, st));
+            MMG_CUDA(cudaMemcpyAsync(out_local_idx, mo.idx, (size_t)total * 4, cudaMemcpyDeviceToHost, st));
+            MMG_CUDA(cudaStreamSynchronize(st));
+        }
+        return MMG_OK;
+    }
     // dense nn_single results + scan scratch + (host callers) the compacted outputs
     const size_t dense = n * 32, scanb = (n + 2 + scan_scratch_elems(n)) * sizeof(u32), comp = mem == MMG_MEM_HOST ? n * 28 : 0;
     char*        ob    = (char*)m->scratch_get(S_MATCH, dense + scanb + comp + 256);
@@ -725,9 +873,7 @@ extern "C" int mmg_match_batch(const mmg_map* cm, const float* xs, const float* 
     char*    cb   = (char*)offs + ((scanb + 63) / 64) * 64;
     if (m->kind == MMG_HASHED_VOXEL)
     {
-        // "d2 < max" as the initial search radius: the largest float below max (nothing when max <= 0)
-        const float bd = std::isinf(max_dist_sqr) && max_dist_sqr > 0 ? INFINITY : std::nextafterf(max_dist_sqr, -INFINITY);
-        rc             = nn_single_voxel<HashedTraits>(m, dx, dy, dz, n, 1, pose12, fnd, xyz, d2, (uint64_t*)id, MMG_MEM_DEVICE, st, bd);
+        rc = nn_single_voxel<HashedTraits>(m, dx, dy, dz, n, 1, pose12, fnd, xyz, d2, (uint64_t*)id, MMG_MEM_DEVICE, st, bd_thr);
     }
     else
     {
@@ -804,6 +950,7 @@ int mmg_create(int kind, const mmg_params* p, int device, mmg_map** out)
     MMG_CUDA(cudaDeviceGetAttribute(&m->num_sms, cudaDevAttrMultiProcessorCount, device));
     MMG_CUDA(cudaMalloc(&m->dev.ctr, sizeof(Counters)));
     MMG_CUDA(cudaMallocHost(&m->h_ctr, sizeof(Counters)));
+    MMG_CUDA(cudaEventCreateWithFlags(&m->ev_ctr, cudaEventDisableTiming));
     {   // the query pipelines take their scratch from the stream-ordered pool: keep freed blocks cached instead of
         // returning them to the driver at every synchronisation
         cudaMemPool_t pool;
@@ -812,7 +959,8 @@ int mmg_create(int kind, const mmg_params* p, int device, mmg_map** out)
         cudaGetLastError();
     }
     int rc = init_counters(m, false);
-    if (!rc && kind != MMG_SPARSE_TREES) rc = alloc_table(m, 1u << 16);
+    if (!rc && kind != MMG_SPARSE_TREES) rc = alloc_table(m, 1u << 16, 0);
+    cudaStreamSynchronize(0);  // the table is usable from any stream once mmg_create returns
     if (!rc && kind == MMG_SPARSE_TREES) rc = trees_create(m);
     if (rc)
     {
@@ -832,6 +980,7 @@ int mmg_destroy(mmg_map* m)
     cudaFree(m->dev.table), cudaFree(m->dev.pts), cudaFree(m->dev.cnt), cudaFree(m->dev.vkey), cudaFree(m->dev.mean), cudaFree(m->dev.free_list), cudaFree(m->dev.fill),
         cudaFree(m->dev.ctr);
     if (m->h_ctr) cudaFreeHost(m->h_ctr);
+    if (m->ev_ctr) cudaEventDestroy(m->ev_ctr);
     if (m->h_stage) cudaFreeHost(m->h_stage);
     if (m->s_in)
     {
@@ -889,9 +1038,17 @@ int mmg_reserve(mmg_map* m, uint64_t voxels)
     return rc;
 }
 
+struct InInsert
+{   // marks the calling thread as inside an insert entry point (MMG_CHECK_MAP then leaves pending counters alone)
+    bool prev;
+    InInsert() : prev(mmg::t_in_insert) { mmg::t_in_insert = true; }
+    ~InInsert() { mmg::t_in_insert = prev; }
+};
+
 int mmg_insert_batch(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, int has_robot_pose, int mem,
                      void* stream)
 {
+    InInsert in_insert;
     MMG_CHECK_MAP(m);
     if (n && (!xs || !ys || !zs)) return MMG_ERR_INVALID_ARG;
     cudaStream_t st = (cudaStream_t)stream;
@@ -906,6 +1063,7 @@ int mmg_insert_batch(mmg_map* m, const float* xs, const float* ys, const float* 
 int mmg_insert_scans(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n_scans, const uint64_t* scan_offsets,
                      const double* poses12, int has_robot_pose, int mem, void* stream)
 {
+    InInsert in_insert;
     MMG_CHECK_MAP(m);
     if (n_scans == 0) return MMG_OK;
     if (!scan_offsets || !poses12) return MMG_ERR_INVALID_ARG;
@@ -958,8 +1116,9 @@ int mmg_insert_scans(mmg_map* m, const float* xs, const float* ys, const float* 
     MMG_CUDA(cudaMemcpyAsync(sb, m->h_stage, sbytes, cudaMemcpyHostToDevice, st));
     ScanSet S{(const PoseD*)sb, (const u32*)(sb + n_scans * sizeof(PoseD)), (u32)n_scans, (float)((double)n_scans / (double)n), make_pose(nullptr)};
     u32     oob = 0;
-    if (m->kind == MMG_HASHED_VOXEL) rc = insert_ranked<HashedTraits>(m, dx, dy, dz, n, S, st, &oob);
-    else rc = insert_ranked<SparseVoxelTraits>(m, dx, dy, dz, n, S, st, &oob);
+    // the pinned staging block of poses / offsets is reused by the next call: an asynchronous return would need it to stay untouched
+    if (m->kind == MMG_HASHED_VOXEL) rc = insert_ranked<HashedTraits>(m, dx, dy, dz, n, S, st, &oob, false);
+    else rc = insert_ranked<SparseVoxelTraits>(m, dx, dy, dz, n, S, st, &oob, false);
     if (rc) return rc;
     m->points_dirty = true;
     if (oob)
@@ -1083,7 +1242,7 @@ int mmg_likelihood(const mmg_map* cm, const float* xs, const float* ys, const fl
     const float *dx, *dy, *dz;
     int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
     if (rc) return rc;
-    char* ob = (char*)m->scratch_get(S_LIK, nq * 32 + 64);
+    char* ob = (char*)m->scratch_get(S_LIK, nq * 32 + 64 + 257 * 8);
     if (!ob) return MMG_ERR_OUT_OF_MEM;
     uint64_t* id  = (uint64_t*)ob;
     float*   xyz = (float*)(ob + nq * 8);
@@ -1096,7 +1255,11 @@ int mmg_likelihood(const mmg_map* cm, const float* xs, const float* ys, const fl
         rc = trees_nn_single(m, dx, dy, dz, n, stride, pose12, fnd, xyz, d2, id, MMG_MEM_DEVICE, st);
     if (rc) return rc;
     const float max_sqr = (float)(m->prm.max_corr_distance * m->prm.max_corr_distance);
-    MMG_LAUNCH(k_likelihood_sum, 1, 1024, 0, st, fnd, d2, (u32)nq, max_sqr, sum);
+    {   // fixed-shape two-level sum (deterministic): up to 256 blocks of 1024 write partials, one block adds them in order
+        const unsigned lb = (unsigned)std::min<size_t>(256, (nq + 4095) / 4096);
+        MMG_LAUNCH(k_likelihood_partial, lb, 1024, 0, st, fnd, d2, (u32)nq, max_sqr, sum + 1);
+        MMG_LAUNCH(k_likelihood_final, 1, 256, 0, st, sum + 1, lb, sum);
+    }
     double h = 0;
     MMG_CUDA(cudaMemcpyAsync(&h, sum, sizeof(double), cudaMemcpyDeviceToHost, st));
     MMG_CUDA(cudaStreamSynchronize(st));
@@ -1108,6 +1271,7 @@ int mmg_is_empty(const mmg_map* m, int* out_empty)
 {
     if (!m || !out_empty) return MMG_ERR_INVALID_ARG;
     if (m->kind == MMG_SPARSE_TREES) return trees_is_empty(m, out_empty);
+    if (int rc = settle(m)) return rc;
     *out_empty = (m->h_nvox_hi - m->h_free_n) == 0;
     return MMG_OK;
 }
@@ -1158,6 +1322,7 @@ int mmg_num_voxels(const mmg_map* m, uint64_t* out_v)
 {
     if (!m || !out_v) return MMG_ERR_INVALID_ARG;
     if (m->kind == MMG_SPARSE_TREES) return trees_num_blocks(m, out_v);
+    if (int rc = settle(m)) return rc;
     *out_v = m->h_nvox_hi - m->h_free_n;
     return MMG_OK;
 }
@@ -1216,21 +1381,33 @@ static int export_voxel(const mmg_map* cm, int32_t* keys, uint32_t* counts, floa
     return MMG_OK;
 }
 
-int mmg_num_points(const mmg_map* m, uint64_t* out_n)
+static __global__ void k_sum_counts(const u32* __restrict__ cnt, u32 nrows, unsigned long long* __restrict__ out)
+{   // rows of evicted voxels hold 0
+    unsigned long long s = 0;
+    for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < nrows; i += gridDim.x * blockDim.x) s += cnt[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(MMG_FULL, s, o);
+    if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+
+int mmg_num_points(const mmg_map* cm, uint64_t* out_n)
 {
-    MMG_CHECK_MAP(m);
+    MMG_CHECK_MAP(cm);
     ScratchScope scratch_scope(nullptr);
+    mmg_map*     m = const_cast<mmg_map*>(cm);
     if (!out_n) return MMG_ERR_INVALID_ARG;
     if (m->kind == MMG_SPARSE_TREES) return trees_num_points(m, out_n);
-    const u64 V = m->h_nvox_hi - m->h_free_n;
-    *out_n      = 0;
-    if (!V) return MMG_OK;
-    std::vector<u32> c(V);
-    int              rc = export_voxel(m, nullptr, c.data(), nullptr, nullptr, nullptr, MMG_MEM_HOST, 0);
-    if (rc) return rc;
-    u64 s = 0;
-    for (u32 x : c) s += x;
-    *out_n = s;
+    *out_n = 0;
+    if (!m->h_nvox_hi) return MMG_OK;
+    // one reduction over the per-row counts on the device, 8 bytes back (round 1 exported every count and summed on the host)
+    unsigned long long* d = (unsigned long long*)m->scratch_get(S_LIK, 64);
+    if (!d) return MMG_ERR_OUT_OF_MEM;
+    MMG_CUDA(cudaMemsetAsync(d, 0, 8, 0));
+    MMG_LAUNCH(k_sum_counts, std::min<unsigned>((m->h_nvox_hi + 255) / 256, (unsigned)m->num_sms * 8), 256, 0, 0, m->dev.cnt, m->h_nvox_hi, d);
+    unsigned long long h = 0;
+    MMG_CUDA(cudaMemcpyAsync(&h, d, 8, cudaMemcpyDeviceToHost, 0));
+    MMG_CUDA(cudaStreamSynchronize(0));
+    *out_n = h;
     return MMG_OK;
 }
 
@@ -1312,7 +1489,7 @@ int mmg_clone(const mmg_map* src, mmg_map** out)
     }
     else
     {
-        if ((rc = alloc_table(m, src->cap)) == MMG_OK && (rc = ensure_rows(m, src->rowcap ? src->rowcap : 1, 0)) == MMG_OK)
+        if ((rc = alloc_table(m, src->cap, 0)) == MMG_OK && (rc = ensure_rows(m, src->rowcap ? src->rowcap : 1, 0)) == MMG_OK)
         {
             // ensure_rows may round up; copy the source extent only
             const u64 rc_rows = src->rowcap, cp = (u64)src->row_points();
@@ -1388,7 +1565,7 @@ int mmg_mean_stencil_points(const mmg_map* cm, const float* xs, const float* ys,
 
 int mmg_set_tuning(const char* key, int value)
 {
-    static const char* names[T_COUNT] = {"nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute"};
+    static const char* names[T_COUNT] = {"nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute", "radius_chunk_hits", "sv_split_hits", "nn_task_minb", "e2e_chunk"};
     for (int i = 0; key && i < T_COUNT; i++)
         if (!strcmp(key, names[i]))
         {

@@ -94,6 +94,14 @@ struct mmg_map
     void*            h_stage = nullptr;  // pinned staging block (scan poses + offsets of mmg_insert_scans)
     size_t           h_stage_bytes = 0;
     bool             points_dirty = false;
+    // Lazy counters of the cap-only insert path: a device-buffer insert returns without waiting for its kernels; the commit
+    // kernel mirrors the counters into h_ctr and ev_ctr marks that moment. h_nvox_hi / h_free_n are exact again after
+    // settle(); until then (h_nvox_hi + pending_points) bounds the rows in use from above.
+    cudaEvent_t       ev_ctr = nullptr;
+    std::atomic<bool> ctr_pending{false};
+    mmg::u64          pending_points = 0;
+    mmg::u32          deferred_oob   = 0;  // out-of-range points of batches whose counters were read late
+    std::mutex        ctr_mtx;
     // SparseTrees
     mmg::TreesState* trees = nullptr;
     // host-buffer pipeline (H2D | kernel | D2H overlapped in chunks), created on first use
@@ -140,10 +148,15 @@ enum Tune
     T_NN_TASK_BLOCKS,   // blocks of 256 per SM of k_nn_tasks
     T_NN_MIN_PIPE,      // batches smaller than this take the single-kernel path (one launch, no scratch)
     T_NN_PERMUTE,       // k_nn_single_pruned: scattered tile order on/off
+    T_RADIUS_CHUNK_HITS,  // SparseTrees radius search: hits per chunk of queries (bounds the 24-byte-per-hit scratch)
+    T_SV_SPLIT_HITS,      // SparseVoxel radius search: hits one pass may index (2^31 - 1); smaller values exercise the splitting
+    T_NN_TASK_MINB,       // k_nn_tasks: resident blocks of 256 per SM it is compiled for (5 | 6 | 8)
+    T_E2E_CHUNK,          // queries per chunk of the two-stream host-buffer path of mmg_nn_single_batch
     T_COUNT
 };
 extern int g_tune[T_COUNT];
-int      alloc_table(mmg_map* m, u64 cap);
+int      settle(const mmg_map* m);  // waits for the counters of asynchronous inserts still in flight (no-op otherwise)
+int      alloc_table(mmg_map* m, u64 cap, cudaStream_t st);
 int      ensure_rows(mmg_map* m, u64 rows, cudaStream_t st);
 int      read_counters(mmg_map* m, Counters* c, cudaStream_t st);
 int      stage_in(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, int mem, cudaStream_t st, const float** dx, const float** dy,

@@ -135,6 +135,7 @@ int mmg_bcast(mmg_map* m, mmg_comm* c, int root, void* stream)
     NcclApi* A = api();
     if (!A || !m || !c) return MMG_ERR_INVALID_ARG;
     MMG_CUDA(cudaSetDevice(m->device));
+    if (int rc0 = settle(m)) return rc0;
     cudaStream_t st = (cudaStream_t)stream;
     // 1) header: sizes and parameters
     BcastHeader* dh = (BcastHeader*)m->scratch_get(S_OUT, sizeof(BcastHeader) + 64);
@@ -176,10 +177,20 @@ int mmg_bcast(mmg_map* m, mmg_comm* c, int root, void* stream)
     {
         m->prm = h.prm;
         m->inv = 1.0f / h.prm.voxel_size;
-        if (m->cap != h.cap && (rc = alloc_table(m, h.cap))) return rc;
+        if (m->cap != h.cap && (rc = alloc_table(m, h.cap, st))) return rc;
         if ((rc = ensure_rows(m, h.rows, st))) return rc;
-        m->h_nvox_hi = h.nvox_hi;
-        m->h_free_n  = h.free_n;
+        // rows the receiver had filled beyond the root's extent would otherwise be handed out again with stale counts
+        if (m->h_nvox_hi > h.rows)
+        {
+            const u64 a = h.rows, k = m->h_nvox_hi - h.rows;
+            MMG_CUDA(cudaMemsetAsync(m->dev.cnt + a, 0, k * sizeof(u32), st));
+            MMG_CUDA(cudaMemsetAsync(m->dev.vkey + a, 0xFF, k * sizeof(u64), st));
+            MMG_CUDA(cudaMemsetAsync(m->dev.fill + a, 0, k * sizeof(u32), st));
+            if (m->kind == MMG_SPARSE_VOXEL) MMG_CUDA(cudaMemsetAsync(m->dev.mean + a, 0, k * sizeof(float4), st));
+        }
+        m->h_nvox_hi    = h.nvox_hi;
+        m->h_free_n     = h.free_n;
+        m->points_dirty = true;
     }
     // 3) the flat buffers, one group
     const u64 cp = (u64)m->row_points();

@@ -365,21 +365,63 @@ namespace mmg
 // so the result is the exhaustive walk's, bit for bit, whatever order the tasks run in.
 struct NNWork
 {
-    float4* qpt;       // composed query points (w unused)
+    float4* qpt;       // composed query points; w = row id of the query's own voxel (bit pattern) when it has one
     u64*    qkey;      // per query {d2 bits : rank}; rank 0xFFFFFFFF = nothing found yet
     u32*    queue[3];  // face / edge / corner tasks: cell (5 bits) << 27 | query (27 bits)
-    u32*    count;     // [3] queue tails
+    u32*    count;     // [0..2] queue tails, [3] ticket of k_nn_finish_match
 };
 constexpr u32 NN_FACE = 0x415410u, NN_EDGE = 0x2aa8aaau, NN_CORNER = 0x7FFFFFFu & ~(NN_FACE | NN_EDGE | (1u << 13));
 constexpr u32 NN_CHUNK = 1u << 20;  // queries per pipeline pass (task ids hold 27 bits; bounds the worst-case queue size)
 constexpr int NN_OWN_BLOCK = 256;
+
+// squared distance from q to the two outer slabs of cell c's axis neighbours (c - 1 and c + 1); the query lies inside cell c,
+// whose own slab contributes 0
+template <class Tr>
+__device__ __forceinline__ void nn_axis_gaps2(int c, float vsize, float q, float& below, float& above)
+{
+    float lo, hi, t;
+    Tr::cell_span(c - 1, t, hi);  // upper end of the cell below
+    Tr::cell_span(c + 1, lo, t);  // lower end of the cell above
+    const float e0 = (fabsf((float)(c - 1)) + 2.0f) * vsize * 1e-6f, e1 = (fabsf((float)(c + 1)) + 2.0f) * vsize * 1e-6f;
+    const float d0 = fmaxf(0.f, q - (hi * vsize + e0)), d1 = fmaxf(0.f, lo * vsize - e1 - q);
+    below = d0 * d0 * 0.9999f, above = d1 * d1 * 0.9999f;
+}
+
+// Two consecutive row slots with one 256-bit load (sm_100 LDG.256): half the load instructions and half the L1 tag
+// look-ups of the row walks, which ncu shows to be the busiest unit of these kernels (7 look-ups per warp load in
+// k_nn_tasks, 0.6 per SM cycle). Rows are 512-byte aligned and s is even, so the pair never straddles a 32-byte boundary.
+__device__ __forceinline__ void ld_row_pair(const float4* p, float4& a, float4& b)
+{
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+        : "l"(p));
+}
+// nearest of the first `cnt` slots of a row: strict '<' in ascending slot order keeps the first minimum
+__device__ __forceinline__ void row_nearest(const float4* __restrict__ row, u32 cnt, const float3& p, float& cd, u32& cs)
+{
+    unsigned long long qxy;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(qxy) : "f"(p.x), "f"(p.y));
+    cd = __int_as_float(0x7f800000);
+    cs = 0;
+#pragma unroll 2
+    for (u32 s = 0; s < cnt; s += 2)
+    {
+        float4 a, b;
+        ld_row_pair(row + s, a, b);
+        const float d0 = sqr_dist_packed(a, qxy, p.z);
+        if (d0 < cd) cd = d0, cs = s;
+        const float d1 = sqr_dist_packed(b, qxy, p.z);
+        if (s + 1 < cnt && d1 < cd) cd = d1, cs = s + 1;
+    }
+}
 
 template <class Tr>
 __global__ void __launch_bounds__(NN_OWN_BLOCK)
     k_nn_own(VoxelMapDev m, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, u32 stride, PoseD pose,
              int use_pose, float inv, float vsize, float bd_init, NNWork w)
 {
-    constexpr int NW = NN_OWN_BLOCK / 32;
+    constexpr int CAP = Tr::CAP;
+    constexpr int NW  = NN_OWN_BLOCK / 32;
     __shared__ u32 s_cnt[3][NW];
     __shared__ u32 s_base[3];
     const int  lane = lane_id(), wid = threadIdx.x >> 5;
@@ -399,18 +441,28 @@ __global__ void __launch_bounds__(NN_OWN_BLOCK)
     u32   br = 0xFFFFFFFFu, bv = 0, t = 0;
     if (ok)
     {
-        float gx[3], gy[3], gz[3];
-        nn_axis_gaps<Tr>(cx, vsize, p.x, gx);
-        nn_axis_gaps<Tr>(cy, vsize, p.y, gy);
-        nn_axis_gaps<Tr>(cz, vsize, p.z, gz);
-        nn_visit_cell<Tr, true>(m, 13, cx, cy, cz, p, bd, br, bv);
+        u32 vid, cnt;
+        if (probe_ro(m.table, m.mask, pack_key(cx, cy, cz), vid, cnt) && cnt)
+        {   // the query's own voxel: rank 13 * 32 + slot
+            float cd;
+            u32   cs;
+            row_nearest(m.pts + (size_t)vid * CAP, cnt, p, cd, cs);
+            if (cd < bd || (cd == bd && 13u * 32u + cs < br)) bd = cd, br = 13u * 32u + cs, bv = vid;
+        }
+        // the neighbour cells whose box can still hold a point at least as close: the box distance separates per axis, and
+        // the query's own slab contributes nothing
+        float g[3][3];
+        nn_axis_gaps2<Tr>(cx, vsize, p.x, g[0][0], g[0][2]);
+        nn_axis_gaps2<Tr>(cy, vsize, p.y, g[1][0], g[1][2]);
+        nn_axis_gaps2<Tr>(cz, vsize, p.z, g[2][0], g[2][2]);
+        g[0][1] = g[1][1] = g[2][1] = 0.f;
 #pragma unroll
         for (int b = 0; b < 27; b++)
-            if (b != 13 && !(gx[b / 9] + gy[(b / 3) % 3] + gz[b % 3] > bd)) t |= 1u << b;
+            if (b != 13 && !(g[0][b / 9] + g[1][(b / 3) % 3] + g[2][b % 3] > bd)) t |= 1u << b;
     }
     if (valid)
     {
-        w.qpt[q]  = make_float4(p.x, p.y, p.z, 0.f);
+        w.qpt[q]  = make_float4(p.x, p.y, p.z, __uint_as_float(bv));
         w.qkey[q] = ((u64)__float_as_uint(bd) << 32) | (u64)br;
     }
     // queue space: per-warp counts -> one atomicAdd per block and queue
@@ -442,7 +494,7 @@ __global__ void __launch_bounds__(NN_OWN_BLOCK)
         for (int i = 0; i < wid; i++) o += s_cnt[k][i];
         u32* Q = w.queue[k];
         for (u32 r = any & TIER[k]; r; r &= r - 1)
-        {   // cell-major inside the warp
+        {   // cell-major inside the warp: consecutive tasks are consecutive scan points looking at the same neighbour cell
             const int b   = __ffs(r) - 1;
             const u32 bal = __ballot_sync(MMG_FULL, (t >> b) & 1u);
             if ((t >> b) & 1u) Q[o + __popc(bal & lt)] = ((u32)b << 27) | q;
@@ -451,8 +503,13 @@ __global__ void __launch_bounds__(NN_OWN_BLOCK)
     }
 }
 
-template <class Tr>
-__global__ void __launch_bounds__(256)
+// One thread per task, the three queues in tier order (face cells, then edges, then corners: the closer cells have
+// tightened a query's bound before its farther ones are looked at). MINB = resident blocks of 256 per SM the kernel is
+// compiled for (register budget): the work is bound by L1 tag look-ups and by latency (task -> query record -> table probe
+// -> row are four dependent loads), so more resident warps hide more of it. A lane whose task is pruned by the re-check
+// or finds no voxel fetches its next task right away instead of idling while the others walk their rows.
+template <class Tr, int MINB>
+__global__ void __launch_bounds__(256, MINB)
     k_nn_tasks(VoxelMapDev m, float inv, float vsize, NNWork w)
 {
     constexpr int CAP     = Tr::CAP;
@@ -462,38 +519,41 @@ __global__ void __launch_bounds__(256)
     {   // unrolled: the queue pointers stay in registers (a dynamic index would put the parameter block on the stack)
         const u32  cnt = w.count[k];
         const u32* Q   = w.queue[k];
-#pragma unroll 1
-        for (u32 i = gtid; i < cnt; i += gstride)
+        u32        i   = gtid;
+        for (;;)
         {
-            const u32    tk = __ldg(Q + i);
-            const u32    q = tk & 0x7FFFFFFu;
-            const int    b = (int)(tk >> 27);
-            const float4 p = __ldg(w.qpt + q);
-            const u64    key0 = __ldcg(w.qkey + q);  // L2: sees what the tasks that finished so far have found
-            int          cx, cy, cz;
-            Tr::to_index(p.x, inv, cx), Tr::to_index(p.y, inv, cy), Tr::to_index(p.z, inv, cz);
-            const int x = cx + b / 9 - 1, y = cy + (b / 3) % 3 - 1, z = cz + b % 3 - 1;
-            if (!index_in_range(x, y, z)) continue;
-            const float bd = __uint_as_float((u32)(key0 >> 32));
-            if (voxel_lower_bound<Tr>(x, y, z, vsize, p.x, p.y, p.z) > bd) continue;
-            u32 vid, c;
-            if (!probe_ro(m.table, m.mask, pack_key(x, y, z), vid, c) || !c) continue;
-            const float4* row = m.pts + (size_t)vid * CAP;
-            if (c > 8) asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 8));
-            if (c > 16) asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 16));
-            if (c > 24) asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 24));
-            unsigned long long qxy;
-            asm("mov.b64 %0, {%1,%2};" : "=l"(qxy) : "f"(p.x), "f"(p.y));
-            float cd = __int_as_float(0x7f800000);
-            u32   cs = 0;
-#pragma unroll 4
-            for (u32 s = 0; s < c; s++)
+            bool   live = false;
+            u32    q = 0, c = 0, vid = 0;
+            int    b = 0;
+            float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+            u64    key0 = 0;
+#pragma unroll 1
+            while (i < cnt)
             {
-                const float d = sqr_dist_packed(__ldg(row + s), qxy, p.z);
-                if (d < cd) cd = d, cs = s;
+                const u32 tk = __ldg(Q + i);
+                i += gstride;
+                q    = tk & 0x7FFFFFFu;
+                b    = (int)(tk >> 27);
+                p    = __ldg(w.qpt + q);
+                key0 = __ldcg(w.qkey + q);  // L2: sees what the tasks that finished so far have found
+                int cx, cy, cz;
+                Tr::to_index(p.x, inv, cx), Tr::to_index(p.y, inv, cy), Tr::to_index(p.z, inv, cz);
+                const int x = cx + b / 9 - 1, y = cy + (b / 3) % 3 - 1, z = cz + b % 3 - 1;
+                if (!index_in_range(x, y, z)) continue;
+                if (voxel_lower_bound<Tr>(x, y, z, vsize, p.x, p.y, p.z) > __uint_as_float((u32)(key0 >> 32))) continue;
+                if (!probe_ro(m.table, m.mask, pack_key(x, y, z), vid, c) || !c) continue;
+                live = true;
+                break;
             }
-            const u64 key = ((u64)__float_as_uint(cd) << 32) | (u64)((u32)b * 32u + cs);
-            if (key < key0) atomicMin(w.qkey + q, key);
+            if (!__any_sync(MMG_FULL, live)) break;
+            if (live)
+            {
+                float cd;
+                u32   cs;
+                row_nearest(m.pts + (size_t)vid * CAP, c, make_float3(p.x, p.y, p.z), cd, cs);
+                const u64 key = ((u64)__float_as_uint(cd) << 32) | (u64)((u32)b * 32u + cs);
+                if (key < key0) atomicMin(w.qkey + q, key);
+            }
         }
     }
 }
@@ -524,8 +584,8 @@ __global__ void __launch_bounds__(256)
             Tr::to_index(p.x, inv, cx), Tr::to_index(p.y, inv, cy), Tr::to_index(p.z, inv, cz);
             const int b = (int)(br >> 5), slot = (int)(br & 31);
             const int x = cx + b / 9 - 1, y = cy + (b / 3) % 3 - 1, z = cz + b % 3 - 1;
-            u32       vid = 0, c;
-            probe_ro(m.table, m.mask, pack_key(x, y, z), vid, c);
+            u32       vid = __float_as_uint(p.w), c;  // own voxel: its row id came along with the query record
+            if (b != 13) probe_ro(m.table, m.mask, pack_key(x, y, z), vid, c);
             t  = __ldg(m.pts + (size_t)vid * CAP + slot);
             id = plain_id<Tr::SLOT_BITS>(x, y, z, slot);
             d2 = __uint_as_float((u32)(key >> 32));
@@ -542,6 +602,110 @@ __global__ void __launch_bounds__(256)
         const int   ww = 32 * k + lane, src = ww / 3, c = ww - 3 * src;
         const float vx = __shfl_sync(MMG_FULL, t.x, src), vy = __shfl_sync(MMG_FULL, t.y, src), vz = __shfl_sync(MMG_FULL, t.z, src);
         if (q0 + (u32)src < n) out.xyz[3 * (size_t)q0 + ww] = c == 0 ? vx : (c == 1 ? vy : vz);
+    }
+}
+
+// k_nn_finish_match: the last stage of the pipeline for mmg_match_batch. The distance threshold is
+// already the initial search radius of k_nn_own, so "found" means "paired"; instead of dense per-query results this stage
+// writes the pairings only, compacted in local-point order, in the same launch: a single-pass scan over tiles of 256
+// queries with decoupled look-back (each tile publishes its count, then sums its predecessors' counts until it meets one
+// whose inclusive prefix is known). 28 bytes leave the SM per KEPT pairing and nothing else.
+struct MatchOut
+{
+    u32*   idx;    // local point index of each pairing
+    float* xyz;    // map point
+    float* d2;
+    u64*   id;
+    u64*   status; // one word per tile, zeroed before the launch: flag (2 bits) | count
+    u32*   ticket; // tile dispenser, zeroed before the launch
+    u32*   total;  // running number of pairings: read by tile 0 (earlier chunks of the batch), written by the last tile
+};
+template <class Tr>
+__global__ void __launch_bounds__(256)
+    k_nn_finish_match(VoxelMapDev m, u32 n, u32 q_base, float inv, NNWork w, MatchOut o)
+{
+    constexpr int CAP = Tr::CAP;
+    constexpr u64 FLAG_A = 1ull << 62, FLAG_P = 2ull << 62, VAL = FLAG_A - 1;
+    __shared__ u32 s_tile, s_wsum[8], s_base;
+    const int      lane = lane_id(), wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_tile = atomicAdd(o.ticket, 1u);
+    __syncthreads();
+    const u32  tile  = s_tile;
+    const u32  q     = tile * 256u + threadIdx.x;
+    const bool valid = q < n;
+    u64        key   = 0;
+    bool       kept  = false;
+    if (valid)
+    {
+        key  = w.qkey[q];
+        kept = (u32)key != 0xFFFFFFFFu;
+    }
+    const u32 bal = __ballot_sync(MMG_FULL, kept);
+    if (lane == 0) s_wsum[wid] = __popc(bal);
+    __syncthreads();
+    u32 before = __popc(bal & ((1u << lane) - 1u)), tile_total = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+    {
+        const u32 c = s_wsum[k];
+        if (k < wid) before += c;
+        tile_total += c;
+    }
+    if (wid == 0)
+    {
+        u32 excl = 0;
+        if (tile == 0)
+        {
+            excl = *o.total;
+            if (lane == 0) atomicExch(o.status, FLAG_P | (u64)(excl + tile_total));
+        }
+        else
+        {
+            if (lane == 0) atomicExch(o.status + tile, FLAG_A | (u64)tile_total);
+            int look = (int)tile - 1;
+            for (;;)
+            {
+                const int i = look - lane;
+                u64       v = FLAG_P;  // tiles before the first count as a known prefix of 0
+                if (i >= 0)
+                    do {
+                        v = *reinterpret_cast<volatile u64*>(o.status + i);
+                    } while ((v >> 62) == 0);
+                const u32 pm = __ballot_sync(MMG_FULL, (v >> 62) == 2);
+                if (pm)
+                {
+                    const int first = __ffs(pm) - 1;  // nearest predecessor with an inclusive prefix
+                    excl += __reduce_add_sync(MMG_FULL, lane <= first ? (u32)(v & VAL) : 0u);
+                    break;
+                }
+                excl += __reduce_add_sync(MMG_FULL, (u32)(v & VAL));
+                look -= 32;
+            }
+            if (lane == 0) atomicExch(o.status + tile, FLAG_P | (u64)(excl + tile_total));
+        }
+        if (lane == 0)
+        {
+            s_base = excl;
+            if (tile == (n + 255u) / 256u - 1u) *o.total = excl + tile_total;
+        }
+    }
+    __syncthreads();
+    if (kept)
+    {
+        const u32    br = (u32)key;
+        const float4 p  = w.qpt[q];
+        int          cx, cy, cz;
+        Tr::to_index(p.x, inv, cx), Tr::to_index(p.y, inv, cy), Tr::to_index(p.z, inv, cz);
+        const int b = (int)(br >> 5), slot = (int)(br & 31);
+        const int x = cx + b / 9 - 1, y = cy + (b / 3) % 3 - 1, z = cz + b % 3 - 1;
+        u32       vid = __float_as_uint(p.w), c;
+        if (b != 13) probe_ro(m.table, m.mask, pack_key(x, y, z), vid, c);
+        const float4 t  = __ldg(m.pts + (size_t)vid * CAP + slot);
+        const size_t at = (size_t)s_base + before;
+        o.idx[at] = q_base + q;
+        o.xyz[3 * at] = t.x, o.xyz[3 * at + 1] = t.y, o.xyz[3 * at + 2] = t.z;
+        o.d2[at] = __uint_as_float((u32)(key >> 32));
+        o.id[at] = plain_id<Tr::SLOT_BITS>(x, y, z, slot);
     }
 }
 }  // namespace mmg

@@ -67,8 +67,98 @@ __global__ void __launch_bounds__(128)
 }
 }  // namespace
 
-int sv_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float r2, size_t maxp_, uint64_t* ooff,
+namespace
+{
+constexpr int SV_SPLIT = -1000;  // internal: the piece has more hits than one pass indexes with 32 bits
+__global__ void k_add_u64(u64* __restrict__ a, size_t n, u64 v)
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < n) a[i] += v;
+}
+}  // namespace
+
+static int sv_radius_once(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float r2, size_t maxp_,
+                          uint64_t* ooff, uint64_t* ototal, int mem, cudaStream_t st);
+
+// A batch whose hit list outgrows one pass (32-bit hit indices in the std::map emulation) is answered in pieces of
+// queries, the pieces' results concatenated (round 1 refused such batches with "split the batch").
+int sv_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float r2, size_t maxp, uint64_t* ooff,
               uint64_t* ototal, int mem, cudaStream_t st)
+{
+    int rc = sv_radius_once(m, xs, ys, zs, n, pose12, r2, maxp, ooff, ototal, mem, st);
+    if (rc != SV_SPLIT) return rc;
+    struct Piece
+    {
+        char* blob;
+        u64   total;
+    };
+    std::vector<Piece> pieces;
+    auto               cleanup = [&] { for (auto& p : pieces) cudaFree(p.blob); };
+    u64                grand = 0;
+    size_t             step  = std::max<size_t>(1, n / 2);
+    for (size_t a = 0; a < n;)
+    {
+        const size_t k = std::min(step, n - a);
+        uint64_t     t = 0;
+        rc             = sv_radius_once(m, xs + a, ys + a, zs + a, k, pose12, r2, maxp, ooff + a, &t, mem, st);
+        if (rc == SV_SPLIT && k > 1)
+        {
+            step = std::max<size_t>(1, k / 2);
+            continue;
+        }
+        if (rc == SV_SPLIT) set_error("nn_radius_search: a single query has more than 2^31 hits"), rc = MMG_ERR_INVALID_ARG;
+        if (rc)
+        {
+            cleanup();
+            return rc;
+        }
+        // offsets of this piece start at the hits before it (entry a + k is rewritten by the next piece's first entry)
+        if (mem == MMG_MEM_HOST)
+            for (size_t i = 0; i <= k; i++) ooff[a + i] += grand;
+        else
+            k_add_u64<<<(unsigned)((k + 256) / 256), 256, 0, st>>>((u64*)(ooff + a), k + 1, grand);
+        Piece p{nullptr, t};
+        if (t)
+        {
+            if (cudaMalloc(&p.blob, t * 24) != cudaSuccess)
+            {
+                cudaGetLastError();
+                cleanup();
+                set_error("cudaMalloc(%llu) failed", (unsigned long long)(t * 24));
+                return MMG_ERR_OUT_OF_MEM;
+            }
+            cudaMemcpyAsync(p.blob, rad_result().id, t * 8, cudaMemcpyDeviceToDevice, st);
+            cudaMemcpyAsync(p.blob + t * 8, rad_result().xyz, t * 12, cudaMemcpyDeviceToDevice, st);
+            cudaMemcpyAsync(p.blob + t * 20, rad_result().d2, t * 4, cudaMemcpyDeviceToDevice, st);
+        }
+        pieces.push_back(p);
+        grand += t;
+        a += k;
+    }
+    char* hb = (char*)m->scratch_get(S_RHITS, std::max<u64>(grand, 1) * 24);
+    if (!hb)
+    {
+        cleanup();
+        return MMG_ERR_OUT_OF_MEM;
+    }
+    u64 at = 0;
+    for (auto& p : pieces)
+        if (p.total)
+        {
+            cudaMemcpyAsync(hb + at * 8, p.blob, p.total * 8, cudaMemcpyDeviceToDevice, st);
+            cudaMemcpyAsync(hb + grand * 8 + at * 12, p.blob + p.total * 8, p.total * 12, cudaMemcpyDeviceToDevice, st);
+            cudaMemcpyAsync(hb + grand * 20 + at * 4, p.blob + p.total * 20, p.total * 4, cudaMemcpyDeviceToDevice, st);
+            at += p.total;
+        }
+    MMG_CUDA(cudaStreamSynchronize(st));
+    cleanup();
+    rad_result().total = grand, rad_result().id = (u64*)hb, rad_result().xyz = (float*)(hb + grand * 8), rad_result().d2 = (float*)(hb + grand * 20);
+    if (ototal) *ototal = grand;
+    return MMG_OK;
+}
+
+static int sv_radius_once(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float r2, size_t maxp_,
+                          uint64_t* ooff, uint64_t* ototal, int mem, cudaStream_t st)
 {
     const float *dx, *dy, *dz;
     int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
@@ -92,11 +182,7 @@ int sv_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, siz
     }
     else
         MMG_CUDA(cudaMemsetAsync(offs, 0, sizeof(u64), st));
-    if (total >= (1ull << 31))
-    {
-        set_error("nn_radius_search batch produced %llu hits (limit 2^31-1): split the batch", (unsigned long long)total);
-        return MMG_ERR_INVALID_ARG;
-    }
+    if (total >= (u64)(unsigned)g_tune[T_SV_SPLIT_HITS]) return SV_SPLIT;
     rad_result().total = total;
     char* hb     = (char*)m->scratch_get(S_RHITS, std::max<u64>(total, 1) * 24);
     if (!hb) return MMG_ERR_OUT_OF_MEM;

@@ -4,6 +4,7 @@
 // :715-741 (boundingBox).
 #include "mmg_hits.cuh"
 #include "mmg_trees.cuh"
+#include "mmg_trees_radius.cuh"
 
 #include <cmath>
 #include <cstring>
@@ -428,6 +429,9 @@ int trees_nn_multi(const mmg_map* cm, const float* xs, const float* ys, const fl
 int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, float r2, size_t maxp_, uint64_t* ooff,
                  uint64_t* ototal, int mem, cudaStream_t st)
 {
+    // see mmg_trees_radius.cuh: count -> (per chunk of queries) hits with unique {d2 : rank} keys -> one thread block per
+    // query sorts its keys in shared memory, applies the per-block maxPoints cut and the std::map collapse, and writes the
+    // survivors at the query's reserved place; a last pass closes the gaps when anything was cut or collapsed.
     TreesState*  s = m->trees;
     const float *dx, *dy, *dz;
     int          rc = stage_in(m, xs, ys, zs, n, mem, st, &dx, &dy, &dz);
@@ -437,74 +441,137 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     // blocks per axis that [q - r, q + r] can touch, +1 for the double-width index 0
     const u64 per_axis = (u64)std::floor(2.0 * r / s->dev.g) + 2;
     const u64 nbq      = per_axis * per_axis * per_axis;
-    if (nbq * (u64)n >= (1ull << 31))
+    if (maxp != 0 && nbq > TRR_NBQ_MAX)
     {
-        set_error("nn_radius_search: radius spans %llu blocks per query x %zu queries; split the batch", (unsigned long long)nbq, n);
+        set_error("nn_radius_search with maxPoints: the radius spans up to %llu blocks per query (limit %u)", (unsigned long long)nbq, TRR_NBQ_MAX);
         return MMG_ERR_INVALID_ARG;
     }
-    const size_t nseg = (size_t)nbq * n;
-    u64*         qoff = (u64*)m->scratch_get(S_ROFF, (n + 2 + scan_scratch_elems(n)) * sizeof(u64));
-    if (!qoff) return MMG_ERR_OUT_OF_MEM;
-    u64 total = 0;
-    MMG_CUDA(cudaMemsetAsync(qoff, 0, (n + 1) * sizeof(u64), st));
+    rad_result().total = 0;
+    const size_t ns = scan_scratch_elems(n);
+    u32*         cnt    = (u32*)m->scratch_get(S_RCNT, (2 * n + 2) * sizeof(u32) + sizeof(TreesRadiusErr) + 64);
+    u64*         off    = (u64*)m->scratch_get(S_ROFF, (n + 2 + ns) * sizeof(u64));
+    u64*         boff   = (u64*)m->scratch_get(S_TREES3, (2 * (n + 2 + ns)) * sizeof(u64));
+    if (!cnt || !off || !boff) return MMG_ERR_OUT_OF_MEM;
+    u32*            bound = cnt + n + 1;
+    u32*            next  = (u32*)(bound + n + 1);
+    TreesRadiusErr* derr  = (TreesRadiusErr*)(next + 2);
+    u64*            noff  = boff + (n + 2 + ns);
+    MMG_CUDA(cudaMemsetAsync(off, 0, (n + 1) * sizeof(u64), st));
+    u64 H = 0, B = 0;
     if (n)
     {
-        u32* counts = (u32*)m->scratch_get(S_RCNT, (nseg + 1) * sizeof(u32));
-        u64* segoff = (u64*)m->scratch_get(S_TREES3, (nseg + 2 + scan_scratch_elems(nseg)) * sizeof(u64));
-        if (!counts || !segoff) return MMG_ERR_OUT_OF_MEM;
         const PoseD    T  = make_pose(pose12);
         const unsigned nb = persistent_blocks(m, n, 8, 8);
-        MMG_LAUNCH((k_trees_radius<0>), nb, 256, 0, st, s->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, r2, r, (u32)nbq, counts, (const u64*)nullptr,
-                   (float*)nullptr, (float*)nullptr, (u32*)nullptr, (u32*)nullptr);
-        exclusive_scan<u32, u64>(counts, segoff, nseg, segoff + nseg, segoff + nseg + 1, st);
-        u64 H = 0;
-        MMG_CUDA(cudaMemcpyAsync(&H, segoff + nseg, sizeof(u64), cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemsetAsync(next, 0, 2 * sizeof(u32) + sizeof(TreesRadiusErr), st));
+        MMG_LAUNCH((k_trees_radius_hits<0>), nb, 256, 0, st, s->dev, dx, dy, dz, 0u, (u32)n, T, pose12 ? 1 : 0, r2, r, cnt, (const u64*)nullptr, 0ull,
+                   (u64*)nullptr, (float*)nullptr, (u32*)nullptr, derr);
+        // the place reserved for a query: all its hits, or at most maxPoints per block of its index box
+        const u64 capq = maxp ? std::min<u64>(nbq * (u64)maxp, 0xFFFFFFFFull) : 0;
+        MMG_LAUNCH(k_trees_radius_bound, (unsigned)((n + 255) / 256), 256, 0, st, cnt, (u32)n, (u32)capq, bound);
+        exclusive_scan<u32, u64>(cnt, off, n, off + n, off + n + 1, st);
+        exclusive_scan<u32, u64>(bound, boff, n, boff + n, boff + n + 1, st);
+        std::vector<u64> hoff(n + 1);
+        TreesRadiusErr   herr;
+        MMG_CUDA(cudaMemcpyAsync(hoff.data(), off, (n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(&B, boff + n, sizeof(u64), cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaMemcpyAsync(&herr, derr, sizeof(herr), cudaMemcpyDeviceToHost, st));
         MMG_CUDA(cudaStreamSynchronize(st));
-        if (H >= (1ull << 31))
+        H = hoff[n];
+        if (herr.rank_overflow)
         {
-            set_error("nn_radius_search batch produced %llu hits (limit 2^31-1): split the batch", (unsigned long long)H);
+            set_error("nn_radius_search: the blocks around a query hold more than 2^32 points");
             return MMG_ERR_INVALID_ARG;
         }
         if (H)
         {
-            // source hits: id (u64) | xyz | d2, plus idx / seg / qkey (u32 each)
-            char* hb   = (char*)m->scratch_get(S_RHITS, H * 24);
-            u32*  aux  = (u32*)m->scratch_get(S_QID, 4 * H * sizeof(u32));
-            u32*  sbuf = (u32*)m->scratch_get(S_HSORT, sort_scratch_words(H) * sizeof(u32));
-            u32*  work = (u32*)m->scratch_get(S_HWORK, hits_work_words(H, n) * sizeof(u32));
-            if (!hb || !aux || !sbuf || !work) return MMG_ERR_OUT_OF_MEM;
-            u64*              sid  = (u64*)hb;
-            float*            sxyz = (float*)(hb + H * 8);
-            float*            sd2  = (float*)(hb + H * 20);
-            u32 *             hidx = aux, *hseg = aux + H, *qkey = aux + 2 * H, *key = aux + 3 * H;
-            const SortScratch ss   = sort_scratch_at(sbuf, H);
-            const unsigned    gH   = (unsigned)((H + 255) / 256);
-            MMG_LAUNCH((k_trees_radius<1>), nb, 256, 0, st, s->dev, dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, r2, r, (u32)nbq, counts, segoff, sxyz, sd2, hidx,
-                       hseg);
-            MMG_LAUNCH(k_trees_idx_to_id, gH, 256, 0, st, hidx, (u32)H, sid);
-            // per block: ascending (d2, index), cut at maxPoints -> order (segment, d2, index)
-            u32 *sk, *p1, *p2, *p3;
-            MMG_LAUNCH(k_hits_gather_u32, gH, 256, 0, st, hidx, (const u32*)nullptr, (u32)H, key);
-            radix_sort_pairs(key, nullptr, H, (u32)std::min<u64>(s->npoints, 0xFFFFFFFFull), ss, &sk, &p1, st);
-            MMG_LAUNCH(k_hits_gather_d2, gH, 256, 0, st, sd2, (const u32*)p1, (u32)H, key);
-            radix_sort_pairs(key, p1, H, 0xFFFFFFFFu, ss, &sk, &p2, st);
-            MMG_LAUNCH(k_hits_gather_u32, gH, 256, 0, st, hseg, (const u32*)p2, (u32)H, key);
-            radix_sort_pairs(key, p2, H, (u32)(nseg - 1), ss, &sk, &p3, st);
-            MMG_LAUNCH(k_trees_trunc_keys, gH, 256, 0, st, sk, p3, segoff, (u32)H, (u32)nbq, maxp, (u32)n, qkey);
-            // p3 lives in the sort scratch that hits_map_semantics is about to reuse: move it out
-            MMG_CUDA(cudaMemcpyAsync(hseg, p3, H * sizeof(u32), cudaMemcpyDeviceToDevice, st));
-            // merge through the std::map<float,...>: equal d2 collapse, last block / highest index wins; not re-truncated
-            if ((rc = hits_map_semantics(m, (u32)n, (u32)H, qkey, hseg, ss, work, sxyz, sd2, sid, 0u, qoff, &total, st))) return rc;
+            char* hb = (char*)m->scratch_get(S_RHITS, B * 24);
+            if (!hb) return MMG_ERR_OUT_OF_MEM;
+            u64*   rid  = (u64*)hb;
+            float* rxyz = (float*)(hb + B * 8);
+            float* rd2  = (float*)(hb + B * 20);
+            // chunks of queries: the hit scratch (24 bytes per hit) stays bounded however many hits the batch has
+            const u64 limit = (u64)std::max(1, g_tune[T_RADIUS_CHUNK_HITS]);
+            std::vector<std::pair<size_t, size_t>> chunks;
+            u64                                    hmax = 0;
+            for (size_t a = 0; a < n;)
+            {
+                size_t e = a + 1;
+                while (e < n && hoff[e + 1] - hoff[a] <= limit) e++;
+                chunks.emplace_back(a, e);
+                hmax = std::max(hmax, hoff[e] - hoff[a]);
+                a    = e;
+            }
+            char* tb = (char*)m->scratch_get(S_QID, hmax * 24 + 64);
+            if (!tb) return MMG_ERR_OUT_OF_MEM;
+            u64*   hkey = (u64*)tb;
+            float* hxyz = (float*)(tb + hmax * 8);
+            u32*   hidx = (u32*)(tb + hmax * 20);
+            // shared memory of the sort kernel: the largest query of the batch, rounded up to a power of two
+            u32 smem_cap = 4096;
+            while (smem_cap < herr.maxcnt && smem_cap < TRR_SMEM_CAP) smem_cap <<= 1;
+            const size_t   smem_bytes = (size_t)smem_cap * 10;
+            const unsigned sblocks    = (unsigned)std::min<size_t>(n, (size_t)m->num_sms * std::max<size_t>(1, (200 * 1024) / (smem_bytes + 9 * 1024)));
+            u64*           gkey = nullptr;
+            u32*           gpos = nullptr;
+            u32            gcap = 0;
+            if (herr.maxcnt > smem_cap)
+            {
+                gcap = 1;
+                while (gcap < herr.maxcnt) gcap <<= 1;
+                char* gs = (char*)m->scratch_get(S_HSORT, (size_t)sblocks * gcap * 12 + 64);
+                if (!gs) return MMG_ERR_OUT_OF_MEM;
+                gkey = (u64*)gs, gpos = (u32*)(gs + (size_t)sblocks * gcap * 8);
+            }
+            static bool attr_set = false;
+            if (!attr_set)
+            {
+                MMG_CUDA(cudaFuncSetAttribute(k_trees_radius_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TRR_SMEM_CAP * 10)));
+                attr_set = true;
+            }
+            u32* outcnt = bound;  // the bounds are in boff by now
+            for (auto& ch : chunks)
+            {
+                const size_t a = ch.first, k = ch.second - ch.first;
+                if (hoff[ch.second] == hoff[a])
+                {
+                    MMG_CUDA(cudaMemsetAsync(outcnt + a, 0, k * sizeof(u32), st));
+                    continue;
+                }
+                MMG_LAUNCH((k_trees_radius_hits<1>), persistent_blocks(m, k, 8, 8), 256, 0, st, s->dev, dx, dy, dz, (u32)a, (u32)k, T, pose12 ? 1 : 0, r2, r,
+                           (u32*)nullptr, (const u64*)off, hoff[a], hkey, hxyz, hidx, derr);
+                MMG_CUDA(cudaMemsetAsync(next, 0, sizeof(u32), st));
+                MMG_LAUNCH(k_trees_radius_sort, (unsigned)std::min<size_t>(k, sblocks), TRR_THREADS, smem_bytes, st, s->dev, dx, dy, dz, (u32)a, (u32)k, T,
+                           pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey, (const float*)hxyz,
+                           (const u32*)hidx, gkey, gpos, gcap, smem_cap, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next);
+            }
+            exclusive_scan<u32, u64>(outcnt, noff, n, noff + n, noff + n + 1, st);
+            u64 tot = 0;
+            MMG_CUDA(cudaMemcpyAsync(&tot, noff + n, sizeof(u64), cudaMemcpyDeviceToHost, st));
+            MMG_CUDA(cudaStreamSynchronize(st));
+            if (tot == B)
+            {   // nothing was cut or collapsed: the reserved places are the final ones
+                rad_result().total = tot, rad_result().id = rid, rad_result().xyz = rxyz, rad_result().d2 = rd2;
+                off = boff;
+            }
+            else
+            {
+                char* pb = (char*)m->scratch_get(S_RHITS2, std::max<u64>(tot, 1) * 24);
+                if (!pb) return MMG_ERR_OUT_OF_MEM;
+                u64*   pid  = (u64*)pb;
+                float* pxyz = (float*)(pb + tot * 8);
+                float* pd2  = (float*)(pb + tot * 20);
+                MMG_LAUNCH(k_trees_radius_pack, persistent_blocks(m, n, 8, 8), 256, 0, st, (u32)n, (const u32*)outcnt, (const u64*)boff, (const u64*)noff,
+                           (const float*)rxyz, (const float*)rd2, (const u64*)rid, pxyz, pd2, pid);
+                rad_result().total = tot, rad_result().id = pid, rad_result().xyz = pxyz, rad_result().d2 = pd2;
+                off = noff;
+            }
+            H = tot;
         }
-        else
-            rad_result().total = 0;
     }
-    else
-        rad_result().total = 0;
     MMG_CUDA(cudaGetLastError());
-    MMG_CUDA(cudaMemcpyAsync(ooff, qoff, (n + 1) * sizeof(u64), mem == MMG_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+    MMG_CUDA(cudaMemcpyAsync(ooff, off, (n + 1) * sizeof(u64), mem == MMG_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
     MMG_CUDA(cudaStreamSynchronize(st));
-    if (ototal) *ototal = total;
+    if (ototal) *ototal = H;
     return MMG_OK;
 }
 

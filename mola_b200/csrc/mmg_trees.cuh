@@ -312,32 +312,6 @@ struct KNNVisitor
 };
 
 // hits with d2 < r2 (nanoflann's strict test): counts them, or writes them at `base`
-template <int PASS>
-struct RadiusVisitor
-{
-    float  q[3], r2;
-    u32    c;
-    u64    base;
-    float *oxyz, *od2;
-    u32*   oidx;
-    __device__ __forceinline__ float bound() const { return r2; }
-    __device__ __forceinline__ void  row(const float4& p, bool valid)
-    {
-        const float d   = valid ? sqr_dist(q[0], q[1], q[2], p.x, p.y, p.z) : 0.f;
-        const bool  hit = valid && d < r2;
-        const u32   m   = __ballot_sync(MMG_FULL, hit);
-        if (PASS && hit)
-        {
-            const u64 o = base + c + __popc(m & ((1u << lane_id()) - 1));
-            oxyz[3 * o] = p.x, oxyz[3 * o + 1] = p.y, oxyz[3 * o + 2] = p.z;
-            od2[o]  = d;
-            oidx[o] = __float_as_uint(p.w);
-        }
-        c += __popc(m);
-    }
-    __device__ __forceinline__ void cell_done() {}
-};
-
 // ------------------------------------------------------------------ queries
 __device__ __forceinline__ bool trees_find_block(const TreesDev& t, float x, float y, float z, int& kx, int& ky, int& kz, u32& bid)
 {
@@ -500,50 +474,6 @@ static __global__ void __launch_bounds__(256)
             }
         }
         if (lane == 0) ocount[q] = nout;
-    }
-}
-
-// nn_radius_search (:645-713), hit generation: blocks coordToOuterIdx(q - r) .. (q + r) in
-// cx, cy, cz order; segment (q, ord) = hits of query q in the ord-th block of its range.
-template <int PASS>
-__global__ void __launch_bounds__(256)
-    k_trees_radius(TreesDev t, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, PoseD pose, int use_pose,
-                   float r2, float r, u32 nbq, u32* __restrict__ counts, const u64* __restrict__ segoff, float* __restrict__ oxyz, float* __restrict__ od2,
-                   u32* __restrict__ oidx, u32* __restrict__ oseg)
-{
-    const int lane   = lane_id();
-    const u32 nwarps = (gridDim.x * blockDim.x) >> 5;
-    for (u32 q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < n; q += nwarps)
-    {
-        float3 p = make_float3(qx[q], qy[q], qz[q]);
-        if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
-        int        a[3], b[3];
-        const bool ok = trees_index(t, __fsub_rn(p.x, r), a[0]) & trees_index(t, __fsub_rn(p.y, r), a[1]) & trees_index(t, __fsub_rn(p.z, r), a[2]) &
-                        trees_index(t, __fadd_rn(p.x, r), b[0]) & trees_index(t, __fadd_rn(p.y, r), b[1]) & trees_index(t, __fadd_rn(p.z, r), b[2]);
-        u32 ord = 0;
-        if (ok && r2 > 0.f)
-            for (int x = a[0]; x <= b[0]; x++)
-                for (int y = a[1]; y <= b[1]; y++)
-                    for (int z = a[2]; z <= b[2]; z++, ord++)
-                    {
-                        if (ord >= nbq) continue;  // cannot happen: nbq bounds the range (host)
-                        const u32 seg = q * nbq + ord;
-                        u32       bid, cnt, c = 0;
-                        if (index_in_range(x, y, z) && probe_ro(t.btab, t.bmask, pack_key(x, y, z), bid, cnt))
-                        {
-                            const BlockGeom     g = trees_geom(t, x, y, z);
-                            RadiusVisitor<PASS> v;
-                            v.q[0] = p.x, v.q[1] = p.y, v.q[2] = p.z, v.r2 = r2, v.c = 0;
-                            v.base = PASS ? segoff[seg] : 0, v.oxyz = oxyz, v.od2 = od2, v.oidx = oidx;
-                            trees_traverse(t, bid, g, v.q, v);
-                            c = v.c;
-                            if (PASS)
-                                for (u32 h = lane; h < c; h += 32) oseg[v.base + h] = seg;
-                        }
-                        if (!PASS && lane == 0) counts[seg] = c;
-                    }
-        if (!PASS)
-            for (u32 o = ord + lane; o < nbq; o += 32) counts[q * nbq + o] = 0;
     }
 }
 
@@ -912,20 +842,5 @@ static __global__ void __launch_bounds__(256)
         row  = t.cnext[row];
         fill = TR_ROW;
     }
-}
-// radius post-processing helpers
-static __global__ void k_trees_trunc_keys(const u32* __restrict__ sseg, const u32* __restrict__ perm, const u64* __restrict__ segoff, u32 H, u32 nbq, u32 maxp,
-                                          u32 nq, u32* __restrict__ qkey)
-{  // hit at sorted position t (source index perm[t]) -> its query key (nq = dropped by the per-block maxPoints cut)
-    const u32 t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= H) return;
-    const u32 seg  = sseg[t];
-    const u32 rank = t - (u32)segoff[seg];
-    qkey[perm[t]]  = (maxp != 0 && rank >= maxp) ? nq : seg / nbq;
-}
-static __global__ void k_trees_idx_to_id(const u32* __restrict__ idx, u32 H, u64* __restrict__ id)
-{
-    const u32 t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t < H) id[t] = (u64)idx[t];
 }
 }  // namespace mmg

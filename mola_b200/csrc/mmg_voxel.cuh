@@ -673,24 +673,40 @@ __global__ void __launch_bounds__(128)
     if (!PASS) counts[q] = c;
 }
 
-// Likelihood tail: sum over the decimated queries of min(d2, max_sqr) in fp64 (fixed tree order).
-static __global__ void __launch_bounds__(1024) k_likelihood_sum(const uint8_t* __restrict__ found, const float* __restrict__ d2, u32 n, float max_sqr, double* out)
+// Likelihood tail: sum over the decimated queries of min(d2, max_sqr) in fp64. Fixed summation shape (block b takes the
+// elements b*1024+t, stride gridDim*1024; warp shuffles, then the warps, then the blocks in order): the same inputs give
+// the same bits on every run.
+__device__ __forceinline__ double block_sum_1024(double s, double* sm)
 {
-    __shared__ double sm[32];
-    double            s = 0;
-    for (u32 i = threadIdx.x; i < n; i += blockDim.x)
-        if (found[i]) s += (double)fminf(d2[i], max_sqr);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(MMG_FULL, s, o);
     if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = s;
     __syncthreads();
+    double r = 0;
     if (threadIdx.x < 32)
     {
-        s = sm[threadIdx.x];
+        r = threadIdx.x < (blockDim.x >> 5) ? sm[threadIdx.x] : 0.0;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(MMG_FULL, s, o);
-        if (threadIdx.x == 0) *out = s;
+        for (int o = 16; o > 0; o >>= 1) r += __shfl_down_sync(MMG_FULL, r, o);
     }
+    return r;
+}
+static __global__ void __launch_bounds__(1024) k_likelihood_partial(const uint8_t* __restrict__ found, const float* __restrict__ d2, u32 n, float max_sqr,
+                                                                    double* __restrict__ partial)
+{
+    __shared__ double sm[32];
+    double            s = 0;
+    for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        if (found[i]) s += (double)fminf(d2[i], max_sqr);
+    s = block_sum_1024(s, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+static __global__ void __launch_bounds__(256) k_likelihood_final(const double* __restrict__ partial, u32 nb, double* __restrict__ out)
+{
+    __shared__ double sm[32];
+    double            s = threadIdx.x < nb ? partial[threadIdx.x] : 0.0;
+    s                   = block_sum_1024(s, sm);
+    if (threadIdx.x == 0) *out = s;
 }
 
 }  // namespace mmg

@@ -259,6 +259,25 @@ class _Map:
         m = int(cnt.value)
         return idx[:m], pts[:m], d2[:m], ids[:m]
 
+    def match_planes_batch(self, xs, ys, zs, pose=None, max_dist_sqr=float("inf"), min_points=5):
+        """Point-to-plane pairing (SparseVoxelPointCloud only; extension): returns (local_idx[m], mean[m,3], normal[m,3],
+        plane_dist[m], eig[m,2]) for the points whose own voxel stores >= min_points points and whose distance to the
+        voxel's running mean is below sqrt(max_dist_sqr), in local-point order."""
+        self._sync_params()
+        mem, st, keep, px, py, pz, n, th = self._xyz(xs, ys, zs)
+        idx = self._alloc(th, (n,), np.uint32, "int32")
+        mean = self._alloc(th, (n, 3), np.float32, "float32")
+        nrm = self._alloc(th, (n, 3), np.float32, "float32")
+        dist = self._alloc(th, (n,), np.float32, "float32")
+        eig = self._alloc(th, (n, 2), np.float32, "float32")
+        cnt = C.c_uint64()
+        pk, pp = capi.pose_ptr(pose)
+        rc = self._lib.mmg_match_planes_batch(self._h, px, py, pz, C.c_size_t(n), pp, C.c_float(max_dist_sqr), C.c_uint32(int(min_points)),
+                                              C.byref(cnt), self._ptr(idx), self._ptr(mean), self._ptr(nrm), self._ptr(dist), self._ptr(eig), mem, st)
+        self._raise_like_reference(rc)
+        m = int(cnt.value)
+        return idx[:m], mean[:m], nrm[:m], dist[:m], eig[:m]
+
     def nn_multiple_search_batch(self, xs, ys, zs, N, pose=None):
         """Batched nn_multiple_search. Returns (count[n], pts[n,N,3], d2[n,N], ids[n,N])."""
         if N <= 0:

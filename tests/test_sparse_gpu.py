@@ -238,3 +238,124 @@ def test_insert_hot_voxels_out_of_order(built, kind, size, cap):
         gm, _ = g.voxel_stats()
         om, _ = o.voxel_stats()
         assert np.array_equal(bits(gm), bits(om))
+
+
+def test_sparse_trees_radius_duplicates_ties_and_chunks(built):
+    """std::map<float> semantics under stress (SparseTreesPointCloud.cpp:663-707, SURVEY N2): thousands of duplicated
+    points (equal d2 inside a block: the highest block-local index survives), mirror images across a block boundary
+    (equal d2 in two blocks: the later block survives), queries with more hits than the sort kernel's shared memory holds
+    (global-memory path), and a batch cut into many chunks of queries by a small hit limit (the round-1 library refused
+    batches of 2^31 hits instead of chunking)."""
+    import ctypes as C
+    from mola_b200 import capi
+    g, o = _pair(2, 10.0, minimum_points_clearance=0.0)
+    rng = np.random.default_rng(11)
+    base = np.stack([rng.uniform(2.0, 8.0, 350), rng.uniform(-3.0, 3.0, 350), rng.uniform(0.0, 2.0, 350)], 1).astype(np.float32)
+    base = np.round(base * 64) / 64                                    # exactly representable offsets
+    mirror = base.copy()
+    mirror[:, 0] = np.float32(10.0) - base[:, 0]                        # x = 5 is the boundary between blocks 0 and 1
+    pts = np.concatenate([np.repeat(base, 60, axis=0), np.repeat(mirror, 60, axis=0)]).astype(np.float32)
+    pts = pts[rng.permutation(pts.shape[0])]
+    xs, ys, zs = (np.ascontiguousarray(pts[:, a]) for a in range(3))
+    g.insert(xs, ys, zs, None)                                          # one batch: no intra-batch clearance test
+    o.insert(xs, ys, zs, None)
+    assert g.num_points() == pts.shape[0] == o.num_points()
+    _same_export(g, o)
+    nq = 240
+    q = [np.full(nq, 5.0, np.float32), rng.uniform(-2, 2, nq).astype(np.float32), rng.uniform(0, 2, nq).astype(np.float32)]
+    q[0][nq // 2:] = rng.uniform(3, 7, nq - nq // 2).astype(np.float32)   # half on the boundary plane, half around it
+    lib = capi.lib()
+    lib.mmg_set_tuning.argtypes = [C.c_char_p, C.c_int]
+    try:
+        for limit in (1 << 26, 300_000):
+            capi.check(lib.mmg_set_tuning(b"radius_chunk_hits", limit))
+            for r, mp in ((6.0, 0), (6.0, 16), (6.0, 100), (1.0, 0), (1.0, 3)):
+                hits = _same_radius(g, o, q, r, mp)
+                assert hits > 0
+        # r = 6 m: every query sees tens of thousands of raw hits (> 16384: global-memory sort) that collapse to <= 700
+        raw = g.nn_radius(*q, np.float32(36.0), 0)
+        assert int(np.diff(raw[0]).max()) <= 700
+    finally:
+        capi.check(lib.mmg_set_tuning(b"radius_chunk_hits", 1 << 26))
+
+
+def test_sparse_voxel_radius_split_batches(built):
+    """A SparseVoxel radius batch whose hit list outgrows one pass is answered in pieces of queries (the round-1 library
+    refused it): forced here with a small per-pass limit, results identical to the single pass and to the reference."""
+    import ctypes as C
+    from mola_b200 import capi
+    g, o = _pair(1, 0.2)
+    for k in range(2):
+        sc = _scan("hdl64", s=1.0 * k, scan_id=k)
+        g.insert(*sc)
+        o.insert(*sc)
+    q = [c[::40].copy() for c in compose_host(sc[3], sc[0] + np.float32(0.03), sc[1], sc[2])]
+    lib = capi.lib()
+    lib.mmg_set_tuning.argtypes = [C.c_char_p, C.c_int]
+    try:
+        for limit in (0x7FFFFFFF, 20_000):
+            capi.check(lib.mmg_set_tuning(b"sv_split_hits", limit))
+            for r, mp in ((0.5, 0), (0.5, 8), (0.3, 2)):
+                assert _same_radius(g, o, q, r, mp) > (20_000 if mp == 0 else 0)
+    finally:
+        capi.check(lib.mmg_set_tuning(b"sv_split_hits", 0x7FFFFFFF))
+
+
+def test_point_to_plane_pairing(built):
+    """Extension: point-to-plane pairing against the per-voxel statistics of a SparseVoxel
+    map, pinned by a CPU restatement: own voxel by round-to-nearest index, >= min_points stored points, distance to the
+    voxel's running mean below the threshold, plane normal = eigenvector of the smallest eigenvalue of the stored points'
+    covariance (numpy eigh, fp64), 1e-5 on the normal (up to the sign convention), the plane distance and the eigenvalues."""
+    from mola_b200 import MapError, HashedVoxelPointCloud, SparseVoxelPointCloud, synth
+    g = SparseVoxelPointCloud(0.4)
+    scans = [_scan("hdl64", s=0.7 * k, scan_id=k) for k in range(3)]
+    for sc in scans:
+        g.insertPointCloud(*sc)
+    keys, counts, pts, cap = g.exportVoxels()
+    mean, _ = g.voxelStats()
+    table = {tuple(k): i for i, k in enumerate(keys.tolist())}
+    xs, ys, zs, pose = scans[1]
+    qpose = synth.perturbed_pose(pose, dx=0.05, dyaw_deg=0.2)
+    sel = slice(0, None, 7)
+    lx, ly, lz = xs[sel].copy(), ys[sel].copy(), zs[sel].copy()
+    q = np.stack(compose_host(qpose, lx, ly, lz), 1)
+    thr2, minp = np.float32(0.09), 6
+    idx, gm, gn, gd, ge = g.match_planes_batch(lx, ly, lz, pose=qpose, max_dist_sqr=float(thr2), min_points=minp)
+    inv = np.float32(1.0) / np.float32(0.4)
+    cell = np.rint(q * inv).astype(np.int64)
+    exp_idx, checked = [], 0
+    j = 0
+    for i in range(q.shape[0]):
+        v = table.get(tuple(cell[i].tolist()))
+        if v is None or counts[v] < minp:
+            continue
+        d = (q[i] - mean[v]).astype(np.float32)
+        if not (np.float32(np.float32(d[0] * d[0] + d[1] * d[1]) + d[2] * d[2]) < thr2):
+            continue
+        P = pts[v, :counts[v]].astype(np.float64)
+        c = P.mean(0)
+        cov = (P - c).T @ (P - c) / (counts[v] - 1)
+        w, V = np.linalg.eigh(cov)
+        if not (w[2] > 0):
+            continue
+        exp_idx.append(i)
+        assert j < idx.size and idx[j] == i, (i, j)
+        assert np.array_equal(bits(gm[j]), bits(mean[v]))
+        assert abs(ge[j, 0] - w[0]) <= 1e-5 * w[2] + 1e-12 and abs(ge[j, 1] - w[1]) <= 1e-5 * w[2] + 1e-12
+        if w[1] - w[0] > 1e-3 * w[2]:  # a well-defined plane: the normal is unique up to sign
+            n = V[:, 0]
+            a = int(np.argmax(np.abs(n)))
+            n = n if n[a] > 0 else -n
+            if abs(abs(n[a]) - np.sort(np.abs(n))[1]) > 1e-3:  # sign convention unambiguous
+                assert np.allclose(gn[j], n, atol=1e-5), (gn[j], n)
+                assert abs(gd[j] - float(n @ (q[i].astype(np.float64) - c))) <= 1e-5
+                checked += 1
+        j += 1
+    assert j == idx.size and len(exp_idx) > 2000 and checked > 1000
+    # device buffers: the same pairings
+    import torch
+    d = [torch.from_numpy(a).cuda() for a in (lx, ly, lz)]
+    r2 = g.match_planes_batch(d[0], d[1], d[2], pose=qpose, max_dist_sqr=float(thr2), min_points=minp)
+    assert np.array_equal(r2[0].cpu().numpy().view(np.uint32), idx) and np.array_equal(bits(r2[2].cpu().numpy()), bits(gn))
+    with pytest.raises(MapError):
+        HashedVoxelPointCloud(0.5).match_planes_batch(lx, ly, lz)

@@ -63,6 +63,24 @@ def main():
             e1.synchronize()
             ms.append(e0.elapsed_time(e1))
         st = None
+        if os.environ.get("AB_E2E"):
+            import time
+            hq = [torch.from_numpy(a).pin_memory() for a in q]
+            ho = [torch.empty(n, dtype=torch.uint8).pin_memory(), torch.empty((n, 3), dtype=torch.float32).pin_memory(),
+                  torch.empty(n, dtype=torch.float32).pin_memory(), torch.empty(n, dtype=torch.int64).pin_memory()]
+
+            def step_host():
+                capi.check(lib.mmg_nn_single_batch(gmap._h, fp(hq[0]), fp(hq[1]), fp(hq[2]), C.c_size_t(n), None, vp(ho[0]), vp(ho[1]),
+                                                   vp(ho[2]), vp(ho[3]), capi.MEM_HOST, sp))
+            for _ in range(3):
+                step_host()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                step_host()
+            torch.cuda.synchronize()
+            st = {"e2e_ms": 1e3 * (time.perf_counter() - t0) / steps, "e2e_same": bool(all(
+                np.array_equal(a.numpy().view(np.uint8), b.cpu().numpy().view(np.uint8)) for a, b in zip(ho, out)))}
         res = [o.cpu().numpy() for o in out]
         same = None
         if ref is None:
