@@ -19,7 +19,7 @@
 namespace mmg
 {
 std::atomic<unsigned long long> g_launches{0};
-int                       g_tune[T_COUNT] = {0, 16, 4096, 1, 1 << 26, 0x7FFFFFFF, 6, 1 << 17};
+int                       g_tune[T_COUNT] = {0, 16, 4096, 1, 1 << 26, 0x7FFFFFFF, 6};
 static thread_local char  g_err[512] = "";
 void set_error(const char* fmt, ...)
 {
@@ -320,9 +320,9 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
     const u32         hard     = (u32)Tr::CAP;
     const bool        uncapped = (P.max_points_per_voxel == 0 || P.max_points_per_voxel > hard);
     const u32         eff      = uncapped ? hard : P.max_points_per_voxel;
-    MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->oob, 0, 2 * sizeof(u32), st));  // oob, nseg: they run on from chunk to chunk
-    static_assert(offsetof(Counters, nseg) == offsetof(Counters, oob) + sizeof(u32), "oob and nseg are cleared by one memset");
-    u32 seg_base = 0, oob = 0;
+    // oob and nseg are zero here: k_insert_commit's last block clears them after mirroring, every other writer cleans up
+    const u32 seg_base = 0;
+    u32       oob      = 0;
     for (size_t a = 0; a < n;)
     {
         int rc;
@@ -366,7 +366,7 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
             MMG_LAUNCH((k_insert_rank<Tr, false>), rb, RANK_BLOCK, 0, st, dx + a, dy + a, dz + a, (u32)k, (u32)a, S, m->inv, m->dev, eff, touched, seg_base,
                        uncapped ? 1 : 0);
         const unsigned fb = persistent_blocks(m, k, 8, 8);
-        MMG_LAUNCH((k_insert_commit<Tr>), fb, 256, 0, st, m->dev, touched, dx + a, dy + a, dz + a, (u32)a, S, m->inv, uncapped ? 0 : 1,
+        launch_pdl(k_insert_commit<Tr>, fb, 256, st, m->dev, (const u32*)touched, dx + a, dy + a, dz + a, (u32)a, S, m->inv, uncapped ? 0 : 1,
                    m->kind == MMG_SPARSE_VOXEL ? 1 : 0, seg_base, m->h_ctr);
         MMG_CUDA(cudaGetLastError());
         // the commit kernel's last block mirrors the counters into the pinned block: an event marks the moment, no copy call
@@ -377,7 +377,6 @@ static int insert_ranked(mmg_map* m, const float* dx, const float* dy, const flo
         if (a < n || !async)
         {   // the next chunk continues the touched-voxel list: it needs this chunk's counters
             if ((rc = settle(m))) return rc;
-            seg_base = m->h_ctr->nseg;
         }
     }
     oob             = m->deferred_oob;  // everything settled so far, earlier asynchronous batches included
@@ -457,6 +456,8 @@ static int insert_voxel(mmg_map* m, const float* xs, const float* ys, const floa
     MMG_LAUNCH((k_fold<Tr>), fb, 256, 0, st, m->dev, svid, sidx, segs, (u32)n, gp, m->inv, P.max_points_per_voxel, use_thr ? thr : 0.f, bbox_acc,
                m->kind == MMG_SPARSE_VOXEL ? 1 : 0);
     MMG_CUDA(cudaGetLastError());
+    MMG_CUDA(cudaMemsetAsync(&m->dev.ctr->oob, 0, 2 * sizeof(u32), st));  // oob, nseg: the cap-only path expects them clear
+    static_assert(offsetof(Counters, nseg) == offsetof(Counters, oob) + sizeof(u32), "oob and nseg are cleared by one memset");
     // this path keeps no lazy counters: calls that read the map on another stream (mmg_bbox, exports) must find it complete
     MMG_CUDA(cudaStreamSynchronize(st));
     m->points_dirty = true;
@@ -479,7 +480,7 @@ struct OutBufs
 
 template <class Tr>
 static int launch_nn_single(const mmg_map* m, const float* dx, const float* dy, const float* dz, size_t nq, size_t stride, const PoseD& T, int use_pose,
-                             const QueryOut& o, cudaStream_t st, float bd_init = INFINITY, const MatchOut* match = nullptr, char* wb_ext = nullptr)
+                             const QueryOut& o, cudaStream_t st, float bd_init = INFINITY, const MatchOut* match = nullptr, bool single_kernel = false)
 {
     // `match` (pipeline only): write compacted pairings through k_nn_finish_match instead of dense results
     // A/B switch for the profiles: MMG_NN_KERNEL = tasks (default) | pruned | grouped | simple, or mmg_set_tuning("nn_kernel", 0..3)
@@ -487,15 +488,15 @@ static int launch_nn_single(const mmg_map* m, const float* dx, const float* dy, 
         const char* e = getenv("MMG_NN_KERNEL");
         return !e ? -1 : (!strcmp(e, "pruned") ? 1 : (!strcmp(e, "grouped") ? 2 : (!strcmp(e, "simple") ? 3 : 0)));
     }();
-    const int kv = env_variant >= 0 ? env_variant : g_tune[T_NN_KERNEL];
+    const int kv = single_kernel ? 1 : (env_variant >= 0 ? env_variant : g_tune[T_NN_KERNEL]);
     if (kv == 0 && nq >= (size_t)g_tune[T_NN_MIN_PIPE])
     {   // three-kernel pipeline over a global task queue (mmg_query.cuh); its scratch comes from the stream-ordered pool, so
         // concurrent callers on one map never share state
         const size_t c0 = std::min<size_t>(nq, NN_CHUNK);
         const size_t off_key = 16 * c0, off_q = off_key + 8 * c0, off_cnt = off_q + 104 * c0, off_status = off_cnt + 32;
         const size_t tiles0 = (c0 + 255) / 256, wbytes = off_status + (match ? tiles0 * 8 : 0);
-        char*        wb = wb_ext;  // a caller that runs several passes on several streams brings its own work buffers
-        if (!wb && cudaMallocAsync((void**)&wb, wbytes, st) != cudaSuccess)
+        char*        wb = nullptr;
+        if (cudaMallocAsync((void**)&wb, wbytes, st) != cudaSuccess)
         {
             cudaGetLastError();
             set_error("cudaMallocAsync(%zu) failed", wbytes);
@@ -507,28 +508,24 @@ static int launch_nn_single(const mmg_map* m, const float* dx, const float* dy, 
         for (size_t a = 0; a < nq; a += NN_CHUNK)
         {
             const u32 k = (u32)std::min<size_t>(NN_CHUNK, nq - a);
-            cudaMemsetAsync(W.count, 0, 16, st);
+            cudaMemsetAsync(W.count, 0, match ? 32 + ((k + 255) / 256) * 8 : 16, st);  // queue tails, ticket (+ the tile status words)
             QueryOut oc{o.found + a, o.xyz + 3 * a, o.d2 + a, o.id + a};
             MMG_LAUNCH((k_nn_own<Tr>), (k + NN_OWN_BLOCK - 1) / NN_OWN_BLOCK, NN_OWN_BLOCK, 0, st, m->dev, dx + a * stride, dy + a * stride, dz + a * stride, k,
                        (u32)stride, T, use_pose, m->inv, m->prm.voxel_size, bd_init, W);
             const unsigned tb = (unsigned)std::min<size_t>(((size_t)k * 26 + 255) / 256, (size_t)m->num_sms * g_tune[T_NN_TASK_BLOCKS]);
-            switch (g_tune[T_NN_TASK_MINB])
-            {
-                case 8: MMG_LAUNCH((k_nn_tasks<Tr, 8>), tb, 256, 0, st, m->dev, m->inv, m->prm.voxel_size, W); break;
-                case 6: MMG_LAUNCH((k_nn_tasks<Tr, 6>), tb, 256, 0, st, m->dev, m->inv, m->prm.voxel_size, W); break;
-                default: MMG_LAUNCH((k_nn_tasks<Tr, 5>), tb, 256, 0, st, m->dev, m->inv, m->prm.voxel_size, W); break;
-            }
+            // the two later stages are programmatic dependent launches: scheduled while the stage before drains
+            if (g_tune[T_NN_TASK_MINB] == 5) launch_pdl(k_nn_tasks<Tr, 5>, tb, 256, st, m->dev, m->inv, m->prm.voxel_size, W);
+            else launch_pdl(k_nn_tasks<Tr, 6>, tb, 256, st, m->dev, m->inv, m->prm.voxel_size, W);
             if (match)
             {
                 MatchOut mo = *match;
                 mo.status = (u64*)(wb + off_status), mo.ticket = W.count + 3;  // count[3] is zeroed with the queue tails
-                MMG_CUDA(cudaMemsetAsync(mo.status, 0, ((k + 255) / 256) * 8, st));
-                MMG_LAUNCH((k_nn_finish_match<Tr>), (k + 255) / 256, 256, 0, st, m->dev, k, (u32)a, m->inv, W, mo);
+                launch_pdl(k_nn_finish_match<Tr>, (k + 255) / 256, 256, st, m->dev, k, (u32)a, m->inv, W, mo);
             }
             else
-                MMG_LAUNCH((k_nn_finish<Tr>), (k + 255) / 256, 256, 0, st, m->dev, k, m->inv, W, oc);
+                launch_pdl(k_nn_finish<Tr>, (k + 255) / 256, 256, st, m->dev, k, m->inv, W, oc);
         }
-        if (!wb_ext) cudaFreeAsync(wb, st);
+        cudaFreeAsync(wb, st);
         return MMG_OK;
     }
     const int variant = kv - 1;
@@ -610,52 +607,13 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
         cudaGetLastError();
         if (all)
         {
-            const float *  hx = (const float*)dp[0], *hy = (const float*)dp[1], *hz = (const float*)dp[2];
-            const QueryOut ho{(uint8_t*)dp[3], (float*)dp[4], (float*)dp[5], (u64*)dp[6]};
-            const size_t   CH = (size_t)std::max(4096, g_tune[T_E2E_CHUNK]);
-            int            rc = MMG_OK;
-            if (nq >= 2 * CH)
-            {   // the pipeline's first stage reads the queries over PCIe and its last one writes the results: chunks alternate
-                // between the caller's stream and an auxiliary one, so the reads of one chunk overlap the writes of another
-                // (both directions of the link busy, as the single-kernel path of round 1 had it)
-                static thread_local struct Aux
-                {
-                    int          dev = -1;
-                    cudaStream_t s   = nullptr;
-                    cudaEvent_t  e0 = nullptr, e1 = nullptr;
-                } aux;
-                if (aux.dev != m->device)
-                {
-                    MMG_CUDA(cudaStreamCreateWithFlags(&aux.s, cudaStreamNonBlocking));
-                    MMG_CUDA(cudaEventCreateWithFlags(&aux.e0, cudaEventDisableTiming));
-                    MMG_CUDA(cudaEventCreateWithFlags(&aux.e1, cudaEventDisableTiming));
-                    aux.dev = m->device;
-                }
-                // one work buffer per stream, both taken from the pool on the caller's stream before the fork and given back
-                // after the join: blocks that move between streams through the pool would chain the streams together
-                const size_t wbytes = 128 * CH + 64;
-                char*        wb2    = nullptr;
-                if (cudaMallocAsync((void**)&wb2, 2 * wbytes, st) != cudaSuccess)
-                {
-                    cudaGetLastError();
-                    set_error("cudaMallocAsync(%zu) failed", 2 * wbytes);
-                    return MMG_ERR_OUT_OF_MEM;
-                }
-                MMG_CUDA(cudaEventRecord(aux.e0, st));
-                MMG_CUDA(cudaStreamWaitEvent(aux.s, aux.e0, 0));
-                int c = 0;
-                for (size_t a = 0; a < nq && !rc; a += CH, c++)
-                {
-                    const size_t k = std::min(CH, nq - a);
-                    rc = launch_nn_single<Tr>(m, hx + a, hy + a, hz + a, k, 1, T, pose12 ? 1 : 0, QueryOut{ho.found + a, ho.xyz + 3 * a, ho.d2 + a, ho.id + a},
-                                              (c & 1) ? aux.s : st, bd_init, nullptr, wb2 + (c & 1) * wbytes);
-                }
-                MMG_CUDA(cudaEventRecord(aux.e1, aux.s));
-                MMG_CUDA(cudaStreamWaitEvent(st, aux.e1, 0));
-                cudaFreeAsync(wb2, st);
-            }
-            else
-                rc = launch_nn_single<Tr>(m, hx, hy, hz, nq, 1, T, pose12 ? 1 : 0, ho, st, bd_init);
+            // ONE kernel (k_nn_single_pruned), not the three-stage pipeline: a kernel that reads its queries and writes its
+            // results keeps both directions of the link busy at once (0.63 ms per 1M queries, link ceiling 0.476 ms,
+            // tools/pcie_probe.py), while the pipeline reads in its first stage and writes in its last (0.84 ms; cutting the
+            // batch into chunks that alternate between two streams did not make the stages of different chunks overlap:
+            // 0.80 - 0.97 ms for chunks of 64k - 512k queries, profiles/r2f_*)
+            const int rc = launch_nn_single<Tr>(m, (const float*)dp[0], (const float*)dp[1], (const float*)dp[2], nq, 1, T, pose12 ? 1 : 0,
+                                                QueryOut{(uint8_t*)dp[3], (float*)dp[4], (float*)dp[5], (u64*)dp[6]}, st, bd_init, nullptr, true);
             if (rc) return rc;
             MMG_CUDA(cudaGetLastError());
             MMG_CUDA(cudaStreamSynchronize(st));
@@ -1565,7 +1523,7 @@ int mmg_mean_stencil_points(const mmg_map* cm, const float* xs, const float* ys,
 
 int mmg_set_tuning(const char* key, int value)
 {
-    static const char* names[T_COUNT] = {"nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute", "radius_chunk_hits", "sv_split_hits", "nn_task_minb", "e2e_chunk"};
+    static const char* names[T_COUNT] = {"nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute", "radius_chunk_hits", "sv_split_hits", "nn_task_minb"};
     for (int i = 0; key && i < T_COUNT; i++)
         if (!strcmp(key, names[i]))
         {

@@ -172,6 +172,7 @@ __global__ void __launch_bounds__(RANK_BLOCK)
     const u32     i     = blockIdx.x * blockDim.x + threadIdx.x;
     const int     lane  = lane_id();
     const bool    valid = i < n;
+    pdl_trigger();  // k_insert_commit (a programmatic dependent launch) may be scheduled while this grid drains
     float         lx = 0.f, ly = 0.f, lz = 0.f;
     if (valid) lx = __ldg(xs + i), ly = __ldg(ys + i), lz = __ldg(zs + i);  // in flight while the scan lookup runs
     BoxNow box;
@@ -311,7 +312,8 @@ __global__ void __launch_bounds__(256)
     constexpr int CAP    = Tr::CAP;
     const int     lane   = lane_id();
     const u32     nwarps = (gridDim.x * blockDim.x) >> 5;
-    const u32     nseg   = m.ctr->nseg - seg_base;  // nseg and oob run on from batch to batch: no memset launches in between
+    pdl_wait();  // everything k_insert_rank wrote is visible from here on
+    const u32     nseg   = m.ctr->nseg - seg_base;  // the list cursor restarts at 0 with every chunk (cleared by the last block below)
     for (u32 t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < nseg; t += nwarps)
     {
         const u32 vid  = touched[t];
@@ -375,6 +377,10 @@ __global__ void __launch_bounds__(256)
             const volatile u32* src = reinterpret_cast<const volatile u32*>(m.ctr);
             for (int k = 0; k < (int)(sizeof(Counters) / sizeof(u32)); k++) dst[k] = src[k];
             __threadfence_system();
+            // the host has this chunk's out-of-range count and list length in the mirror: restart both for the next chunk
+            // (no memset launch per call; every other block has passed its last read of nseg when `done` is complete)
+            m.ctr->oob  = 0;
+            m.ctr->nseg = 0;
         }
     }
 }

@@ -422,6 +422,7 @@ __global__ void __launch_bounds__(NN_OWN_BLOCK)
 {
     constexpr int CAP = Tr::CAP;
     constexpr int NW  = NN_OWN_BLOCK / 32;
+    pdl_trigger();  // k_nn_tasks may be scheduled as soon as the last blocks of this grid are resident; it waits before reading
     __shared__ u32 s_cnt[3][NW];
     __shared__ u32 s_base[3];
     const int  lane = lane_id(), wid = threadIdx.x >> 5;
@@ -514,6 +515,8 @@ __global__ void __launch_bounds__(256, MINB)
 {
     constexpr int CAP     = Tr::CAP;
     const u32     gtid    = blockIdx.x * blockDim.x + threadIdx.x, gstride = gridDim.x * blockDim.x;
+    pdl_trigger();
+    pdl_wait();  // everything k_nn_own wrote (query records, keys, queues, tails) is visible from here on
 #pragma unroll
     for (int k = 0; k < 3; k++)
     {   // unrolled: the queue pointers stay in registers (a dynamic index would put the parameter block on the stack)
@@ -564,6 +567,7 @@ __global__ void __launch_bounds__(256)
 {
     constexpr int CAP  = Tr::CAP;
     const int     lane = lane_id();
+    pdl_wait();
     const u32     q0   = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u;
     const u32     q    = q0 + (u32)lane;
     if (q0 >= n) return;
@@ -628,6 +632,7 @@ __global__ void __launch_bounds__(256)
     constexpr u64 FLAG_A = 1ull << 62, FLAG_P = 2ull << 62, VAL = FLAG_A - 1;
     __shared__ u32 s_tile, s_wsum[8], s_base;
     const int      lane = lane_id(), wid = threadIdx.x >> 5;
+    pdl_wait();
     if (threadIdx.x == 0) s_tile = atomicAdd(o.ticket, 1u);
     __syncthreads();
     const u32  tile  = s_tile;

@@ -16,6 +16,27 @@ extern std::atomic<unsigned long long> g_launches;  // kernels launched by this 
         ++::mmg::g_launches;                                            \
     } while (0)
 
+// Programmatic dependent launch (sm_90+): the kernel may be scheduled while its predecessor in the stream is still
+// draining; it calls pdl_wait() before touching anything the predecessor wrote, and the predecessor calls pdl_trigger()
+// as early as it likes. Hides the launch gap between the short stages of a pipeline.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(grid, 1, 1);
+    cfg.blockDim           = dim3(block, 1, 1);
+    cfg.stream             = st;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    cfg.numAttrs                                     = 1;
+    ++g_launches;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ------------------------------------------------------------------ scan
 constexpr int SCAN_THREADS = 1024, SCAN_ITEMS = 4, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
