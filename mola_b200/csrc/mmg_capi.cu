@@ -14,12 +14,13 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <string>
 #include <vector>
 
 namespace mmg
 {
 std::atomic<unsigned long long> g_launches{0};
-int                       g_tune[T_COUNT] = {0, 16, 4096, 1, 1 << 26, 0x7FFFFFFF, 6};
+int                       g_tune[T_COUNT] = {0, 16, 4096, 1, 1 << 26, 0x7FFFFFFF, 6, 2048};
 static thread_local char  g_err[512] = "";
 void set_error(const char* fmt, ...)
 {
@@ -900,6 +901,25 @@ int mmg_create(int kind, const mmg_params* p, int device, mmg_map** out)
         return MMG_ERR_INVALID_ARG;
     }
     MMG_CUDA(cudaSetDevice(device));
+    static const bool tuned = [] {  // MMG_TUNE="knob=value,knob=value": the mmg_set_tuning() switches from the environment (profiling runs)
+        const char* e = getenv("MMG_TUNE");
+        if (e)
+        {
+            std::string str(e);
+            size_t      a = 0;
+            while (a < str.size())
+            {
+                size_t     b  = str.find(',', a);
+                const auto kv = str.substr(a, b == std::string::npos ? std::string::npos : b - a);
+                const auto eq = kv.find('=');
+                if (eq != std::string::npos) mmg_set_tuning(kv.substr(0, eq).c_str(), atoi(kv.c_str() + eq + 1));
+                if (b == std::string::npos) break;
+                a = b + 1;
+            }
+        }
+        return true;
+    }();
+    (void)tuned;
     mmg_map* m = new mmg_map();
     m->kind    = kind;
     m->device  = device;
@@ -1523,7 +1543,7 @@ int mmg_mean_stencil_points(const mmg_map* cm, const float* xs, const float* ys,
 
 int mmg_set_tuning(const char* key, int value)
 {
-    static const char* names[T_COUNT] = {"nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute", "radius_chunk_hits", "sv_split_hits", "nn_task_minb"};
+    static const char* names[T_COUNT] = {"nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute", "radius_chunk_hits", "sv_split_hits", "nn_task_minb", "radius_warp_max"};
     for (int i = 0; key && i < T_COUNT; i++)
         if (!strcmp(key, names[i]))
         {

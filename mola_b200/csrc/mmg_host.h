@@ -151,6 +151,7 @@ enum Tune
     T_RADIUS_CHUNK_HITS,  // SparseTrees radius search: hits per chunk of queries (bounds the 24-byte-per-hit scratch)
     T_SV_SPLIT_HITS,      // SparseVoxel radius search: hits one pass may index (2^31 - 1); smaller values exercise the splitting
     T_NN_TASK_MINB,       // k_nn_tasks: resident blocks of 256 per SM it is compiled for (5 | 6 | 8)
+    T_RADIUS_WARP_MAX,    // SparseTrees radius search: lists up to this many hits are sorted by a warp, longer ones by a block
     T_COUNT
 };
 extern int g_tune[T_COUNT];

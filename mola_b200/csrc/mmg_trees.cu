@@ -7,6 +7,7 @@
 #include "mmg_trees_radius.cuh"
 
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 
 using namespace mmg;
@@ -501,33 +502,18 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
                 hmax = std::max(hmax, hoff[e] - hoff[a]);
                 a    = e;
             }
-            char* tb = (char*)m->scratch_get(S_QID, hmax * 24 + 64);
+            // per hit: key 8 + point 12 + index 4 from the hit pass, and two (key, hit) sort buffers of 12 bytes each
+            char* tb = (char*)m->scratch_get(S_QID, hmax * 48 + 64);
             if (!tb) return MMG_ERR_OUT_OF_MEM;
             u64*   hkey = (u64*)tb;
-            float* hxyz = (float*)(tb + hmax * 8);
-            u32*   hidx = (u32*)(tb + hmax * 20);
-            // shared memory of the sort kernel: the largest query of the batch, rounded up to a power of two
-            u32 smem_cap = 4096;
-            while (smem_cap < herr.maxcnt && smem_cap < TRR_SMEM_CAP) smem_cap <<= 1;
-            const size_t   smem_bytes = (size_t)smem_cap * 10;
-            const unsigned sblocks    = (unsigned)std::min<size_t>(n, (size_t)m->num_sms * std::max<size_t>(1, (200 * 1024) / (smem_bytes + 9 * 1024)));
-            u64*           gkey = nullptr;
-            u32*           gpos = nullptr;
-            u32            gcap = 0;
-            if (herr.maxcnt > smem_cap)
-            {
-                gcap = 1;
-                while (gcap < herr.maxcnt) gcap <<= 1;
-                char* gs = (char*)m->scratch_get(S_HSORT, (size_t)sblocks * gcap * 12 + 64);
-                if (!gs) return MMG_ERR_OUT_OF_MEM;
-                gkey = (u64*)gs, gpos = (u32*)(gs + (size_t)sblocks * gcap * 8);
-            }
-            static bool attr_set = false;
-            if (!attr_set)
-            {
-                MMG_CUDA(cudaFuncSetAttribute(k_trees_radius_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TRR_SMEM_CAP * 10)));
-                attr_set = true;
-            }
+            u64*   bufk = hkey + hmax;                       // 2 * hmax keys
+            float* hxyz = (float*)(tb + hmax * 24);
+            u32*   hidx = (u32*)(tb + hmax * 36);
+            u32*   bufp = (u32*)(tb + hmax * 40);            // 2 * hmax hit numbers
+            const unsigned sblocks = (unsigned)std::min<size_t>((n + TRR_WARPS - 1) / TRR_WARPS, (size_t)m->num_sms * 6);
+            const u32      nbq32   = (u32)std::max<u64>(1, std::min<u64>(nbq, TRR_NBQ_MAX));
+            u32*           gtab    = (u32*)m->scratch_get(S_HSORT, (size_t)sblocks * TRR_WARPS * 2 * nbq32 * sizeof(u32) + 64);
+            if (!gtab) return MMG_ERR_OUT_OF_MEM;
             u32* outcnt = bound;  // the bounds are in boff by now
             for (auto& ch : chunks)
             {
@@ -539,10 +525,34 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
                 }
                 MMG_LAUNCH((k_trees_radius_hits<1>), persistent_blocks(m, k, 8, 8), 256, 0, st, s->dev, dx, dy, dz, (u32)a, (u32)k, T, pose12 ? 1 : 0, r2, r,
                            (u32*)nullptr, (const u64*)off, hoff[a], hkey, hxyz, hidx, derr);
-                MMG_CUDA(cudaMemsetAsync(next, 0, sizeof(u32), st));
-                MMG_LAUNCH(k_trees_radius_sort, (unsigned)std::min<size_t>(k, sblocks), TRR_THREADS, smem_bytes, st, s->dev, dx, dy, dz, (u32)a, (u32)k, T,
-                           pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey, (const float*)hxyz,
-                           (const u32*)hidx, gkey, gpos, gcap, smem_cap, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next);
+                MMG_CUDA(cudaMemsetAsync(next, 0, 2 * sizeof(u32), st));
+                // short lists: a warp per query over L2-resident scratch; long ones: a block per query in shared memory
+                const u32 n_small = (u32)std::max(0, g_tune[T_RADIUS_WARP_MAX]);
+                const u32 n_large = herr.maxcnt > n_small ? std::min<u32>(TRB_CAP, (herr.maxcnt + 1023u) & ~1023u) : n_small;
+                MMG_LAUNCH(k_trees_radius_sort, (unsigned)std::min<size_t>((k + TRR_WARPS - 1) / TRR_WARPS, sblocks), TRR_THREADS, 0, st, s->dev, dx, dy, dz,
+                           (u32)a, (u32)k, T, pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey,
+                           (const float*)hxyz, (const u32*)hidx, bufk, bufp, hmax, gtab, nbq32, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next, n_small,
+                           n_large);
+                if (n_large > n_small)
+                {
+                    static bool attr_set = false;
+                    if (!attr_set)
+                    {
+                        MMG_CUDA(cudaFuncSetAttribute(k_trees_radius_sort_block, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TRB_CAP * 12)));
+                        attr_set = true;
+                    }
+                    const size_t   smem = (size_t)n_large * 12;
+                    const unsigned bpsm = (unsigned)std::max<size_t>(1, std::min<size_t>(4, (220 * 1024) / (smem + 26 * 1024)));
+                    MMG_LAUNCH(k_trees_radius_sort_block, (unsigned)std::min<size_t>(k, (size_t)m->num_sms * bpsm), TRB_THREADS, smem, st, s->dev, dx, dy, dz,
+                               (u32)a, (u32)k, T, pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey,
+                               (const float*)hxyz, (const u32*)hidx, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next + 1, n_small, n_large);
+                    if (getenv("MMG_DEBUG"))
+                    {
+                        cudaError_t e = cudaStreamSynchronize(st);
+                        fprintf(stderr, "[trees_radius] maxcnt %u n_small %u n_large %u smem %zu bpsm %u -> %s / %s\n", herr.maxcnt, n_small, n_large, smem, bpsm,
+                                cudaGetErrorString(e), cudaGetErrorString(cudaGetLastError()));
+                    }
+                }
             }
             exclusive_scan<u32, u64>(outcnt, noff, n, noff + n, noff + n + 1, st);
             u64 tot = 0;

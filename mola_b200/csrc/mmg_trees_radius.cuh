@@ -11,24 +11,22 @@
 //   k_trees_radius_hits<1>  same walk, writes per hit a UNIQUE 64-bit key {d2 bits : rank} with
 //                           rank = (points of the blocks visited before this one) + block-local index, i.e. the order the
 //                           reference inserts into its map, plus the point and its index
-//   k_trees_radius_sort     one thread block per query: bitonic sort of the query's keys in shared memory (the hits of
-//                           one query, ~5000 at r = 2 m on the 50 M-point map, never leave the SM), the maxPoints cut per
-//                           block as one warp's in-order walk with per-block counters, keep-last-of-equal-d2, and the
-//                           survivors written once, in order, at the query's place of the result
-// Queries with more hits than fit in shared memory take the same code over global-memory scratch.
+//   k_trees_radius_sort     one warp per query: stable radix sort of the query's (key, hit) pairs in L2-resident scratch
+//                           (~5000 hits per query at r = 2 m on the 50 M-point map), the maxPoints cut per block as an
+//                           in-order walk with per-block counters, keep-last-of-equal-d2, and the survivors written once,
+//                           in order, at the query's place of the result
 #pragma once
 #include "mmg_trees.cuh"
 
 namespace mmg
 {
-constexpr int TRR_THREADS = 512;
-constexpr u32 TRR_SMEM_CAP = 16384;  // keys of one query held in shared memory (10 bytes each)
+constexpr int TRR_THREADS = 256;
 constexpr u32 TRR_NBQ_MAX  = 1024;   // blocks per query the maxPoints walk keeps counters for
 
 struct TreesRadiusErr
 {
     u32 rank_overflow;  // the blocks of one query hold >= 2^32 points (cannot happen below 4 G points per neighbourhood)
-    u32 maxcnt;         // largest per-query hit count (chooses the sort kernel's shared-memory size)
+    u32 maxcnt;         // largest per-query hit count when above 1024 (sizes the block kernel's shared memory)
 };
 
 template <int PASS>
@@ -102,7 +100,7 @@ __global__ void __launch_bounds__(256)
         if (!PASS && lane == 0)
         {
             cnt[w] = v.c;
-            if (v.c > TRR_SMEM_CAP / 4) atomicMax(&err->maxcnt, v.c);
+            if (v.c > 1024u) atomicMax(&err->maxcnt, v.c);
         }
     }
 }
@@ -113,59 +111,179 @@ static __global__ void k_trees_radius_bound(const u32* __restrict__ cnt, u32 n, 
     if (q < n) bound[q] = cap_per_query ? min(cnt[q], cap_per_query) : cnt[q];
 }
 
-// in-place bitonic sort of P = 2^k (key, payload) pairs by one thread block; keys are unique except for the padding
-template <class PosT>
-__device__ __forceinline__ void block_bitonic(u64* __restrict__ key, PosT* __restrict__ pos, u32 P)
+// ---------------------------------------------------------------------------------------------------------------------
+// k_trees_radius_sort: one WARP per query (queries handed out by a counter), everything in L2-resident global scratch.
+// (Round 2 history, all exact: one thread BLOCK per query with the list in shared memory, first as a bitonic network
+// (1100 instructions per hit), then as a shared-memory radix sort: 120 ms for the 1 G hits of the r = 2 m sweep either way,
+// because one query's passes are a chain of dependent shared-memory round trips and the block is the only one on its SM:
+// issue slots 19 % busy, ncu profiles/r2h_*. With a warp per query 48 such chains run per SM.)
+// Stable LSD radix sort, 8-bit digits, of (key, hit) pairs: the d2 half of the key first (digits on which all keys agree
+// are skipped: usually 3 passes); squared distances of different points are almost never bit-equal, so only a list that
+// then shows two equal neighbours is sorted again on the whole key, which puts the members of every tie in the reference's
+// insertion order. Per pass: digit histogram in the warp's 1 KB of shared memory, exclusive scan by the warp, scatter 32
+// pairs at a time, equal digits of a group ranked with __match_any_sync.
+constexpr int TRR_WARPS = TRR_THREADS / 32;
+struct HitBuf
 {
-    for (u32 k = 2; k <= P; k <<= 1)
-        for (u32 j = k >> 1; j > 0; j >>= 1)
+    u64* k;
+    u32* p;
+};
+__device__ __forceinline__ void warp_radix_pass(const u64* __restrict__ sk, const u32* __restrict__ sp /*nullable: identity*/, HitBuf dst, u32 N, int shift,
+                                                u32* hist)
+{
+    const int lane = lane_id();
+#pragma unroll
+    for (int e = 0; e < 8; e++) hist[lane * 8 + e] = 0;
+    __syncwarp();
+    for (u32 i = lane; i < N; i += 32) atomicAdd(&hist[(u32)((sk[i] >> shift) & 0xFFull)], 1u);
+    __syncwarp();
+    {
+        u32 v[8], sum = 0;
+#pragma unroll
+        for (int e = 0; e < 8; e++) v[e] = hist[lane * 8 + e], sum += v[e];
+        u32 incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
         {
-            for (u32 i = threadIdx.x; i < (P >> 1); i += blockDim.x)
-            {
-                const u32  lo = ((i & ~(j - 1)) << 1) | (i & (j - 1)), hi = lo | j;
-                const bool up = (lo & k) == 0;
-                const u64  a = key[lo], b = key[hi];
-                if ((a > b) == up)
-                {
-                    key[lo] = b, key[hi] = a;
-                    const PosT t = pos[lo];
-                    pos[lo]      = pos[hi];
-                    pos[hi]      = t;
-                }
-            }
-            __syncthreads();
+            const u32 y = __shfl_up_sync(MMG_FULL, incl, o);
+            if (lane >= o) incl += y;
         }
+        u32 base = incl - sum;
+#pragma unroll
+        for (int e = 0; e < 8; e++) hist[lane * 8 + e] = base, base += v[e];
+    }
+    __syncwarp();
+    for (u32 b0 = 0; b0 < N; b0 += 32)
+    {
+        const u32  i     = b0 + lane;
+        const bool valid = i < N;
+        const u64  k     = valid ? sk[i] : 0ull;
+        const u32  p     = valid ? (sp ? sp[i] : i) : 0u;
+        const u32  d     = valid ? (u32)((k >> shift) & 0xFFull) : 256u;
+        const u32  peers = __match_any_sync(MMG_FULL, d);
+        if (valid)
+        {
+            const u32 at = hist[d] + __popc(peers & ((1u << lane) - 1u));
+            dst.k[at]    = k;
+            dst.p[at]    = p;
+        }
+        __syncwarp();
+        if (valid && lane == __ffs(peers) - 1) hist[d] += __popc(peers);
+        __syncwarp();
+    }
+}
+// sorts the N pairs (key[i], i) on the key bits [first_shift, 64); returns the buffer that holds the result
+__device__ __forceinline__ HitBuf warp_radix_sort(const u64* __restrict__ key, HitBuf A, HitBuf B, u32 N, int first_shift, u32* hist)
+{
+    const int lane = lane_id();
+    u64       a = ~0ull, o = 0ull;
+    for (u32 i = lane; i < N; i += 32)
+    {
+        const u64 k = key[i];
+        a &= k, o |= k;
+    }
+    const u32 dlo = __reduce_and_sync(MMG_FULL, (u32)a) ^ __reduce_or_sync(MMG_FULL, (u32)o);
+    const u32 dhi = __reduce_and_sync(MMG_FULL, (u32)(a >> 32)) ^ __reduce_or_sync(MMG_FULL, (u32)(o >> 32));
+    const u64 diff = ((u64)dhi << 32) | (u64)dlo;
+    const u64* sk  = key;
+    const u32* sp  = nullptr;
+    HitBuf     dst = A, other = B;
+    for (int shift = first_shift; shift < 64; shift += 8)
+    {
+        if (((diff >> shift) & 0xFFull) == 0) continue;
+        warp_radix_pass(sk, sp, dst, N, shift, hist);
+        sk = dst.k, sp = dst.p;
+        const HitBuf t = dst;
+        dst            = other;
+        other          = t;
+    }
+    if (!sp)
+    {   // no digit varied (one hit, or all keys equal on these bits): the input order is the sorted order
+        for (u32 i = lane; i < N; i += 32) A.k[i] = key[i], A.p[i] = i;
+        __syncwarp();
+        return A;
+    }
+    return other;  // the buffer written last
 }
 
-// One thread block per query (grid-stride over the chunk's queries, heaviest-agnostic: the sort cost is per query).
-// skey/spos: shared memory for up to smem_cap keys; gkey/gpos: global scratch, gcap keys per thread block, for the queries
-// that do not fit.
-template <class PosT, u32 FLAG_BITS>
-__device__ __forceinline__ void trees_radius_finish(const TreesDev& t, u64* __restrict__ key, PosT* __restrict__ pos, u32 N, u32 maxp, u32* s_rank0,
-                                                    u32* s_cnt, u32 nblk, const float* __restrict__ hxyz, const u32* __restrict__ hidx, u64 obase,
-                                                    float* __restrict__ rxyz, float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt_q,
-                                                    u32* s_scan)
+__global__ void __launch_bounds__(TRR_THREADS)
+    k_trees_radius_sort(TreesDev t, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 q0, u32 n, PoseD pose,
+                        int use_pose, float r, u32 maxp, const u32* __restrict__ cnt /*chunk relative*/, const u64* __restrict__ off, u64 off_base,
+                        const u64* __restrict__ key, const float* __restrict__ hxyz, const u32* __restrict__ hidx, u64* __restrict__ bufk,
+                        u32* __restrict__ bufp, u64 hc /*hits of the chunk: bufk / bufp hold two buffers of that length*/, u32* __restrict__ gtab,
+                        u32 nbq /*gtab: 2 * nbq words per warp of the grid*/, const u64* __restrict__ boff, float* __restrict__ rxyz,
+                        float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt, u32* __restrict__ next_query, u32 n_small, u32 n_large)
 {
-    constexpr PosT ACC = (PosT)1 << (FLAG_BITS - 1), SURV = (PosT)1 << (FLAG_BITS - 2), IDX = SURV - 1;
-    const int      lane = lane_id(), wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    if (maxp == 0)
-    {   // every hit enters the map: the last of each run of equal d2 survives
-        for (u32 i = threadIdx.x; i < N; i += blockDim.x)
-            if (i + 1 >= N || (u32)(key[i] >> 32) != (u32)(key[i + 1] >> 32)) pos[i] |= SURV;
-    }
-    else
+    // this kernel takes the queries with at most n_small hits (their lists stay in L2 however many warps run) and those with
+    // more than n_large (too long for the block kernel's shared memory); k_trees_radius_sort_block takes the ones in between
+    constexpr u32  ACC = 1u << 31, SURV = 1u << 30, IDX = SURV - 1u;
+    __shared__ u32 s_hist[TRR_WARPS][256];
+    const int      lane = lane_id(), wid = threadIdx.x >> 5;
+    u32*           hist  = s_hist[wid];
+    u32*           rank0 = gtab + (size_t)(blockIdx.x * TRR_WARPS + wid) * 2 * nbq;
+    u32*           bcnt  = rank0 + nbq;
+    for (;;)
     {
-        // the per-block cut: in ascending (d2, rank) order a hit is taken while its block has handed out fewer than maxPoints;
-        // one warp walks the sorted list 32 at a time with per-block counters (ranks of one block are consecutive, so the
-        // block of a hit is found by searching the blocks' first ranks)
-        if (wid == 0)
+        u32 w = 0;
+        if (lane == 0) w = atomicAdd(next_query, 1u);
+        w = __shfl_sync(MMG_FULL, w, 0);
+        if (w >= n) break;
+        const u32 q = q0 + w, N = cnt[w];
+        if (N == 0)
         {
-            u32 pend = 0xFFFFFFFFu, pend_d2 = 0;  // last accepted hit so far: survives unless the next accepted one has its d2
+            if (lane == 0) outcnt[w] = 0;
+            continue;
+        }
+        if (N > n_small && N <= n_large) continue;
+        const u64    h0 = off[q] - off_base;
+        const HitBuf A{bufk + h0, bufp + h0}, B{bufk + hc + h0, bufp + hc + h0};
+        HitBuf       S = warp_radix_sort(key + h0, A, B, N, 32, hist);
+        __syncwarp();
+        {
+            bool tie = false;
+            for (u32 i = lane; i + 1 < N; i += 32) tie |= (u32)(S.k[i] >> 32) == (u32)(S.k[i + 1] >> 32);
+            if (__any_sync(MMG_FULL, tie)) S = warp_radix_sort(key + h0, A, B, N, 0, hist);
+            __syncwarp();
+        }
+        if (maxp == 0)
+        {   // every hit enters the map: the last of each run of equal d2 survives
+            for (u32 i = lane; i < N; i += 32)
+                if (i + 1 >= N || (u32)(S.k[i] >> 32) != (u32)(S.k[i + 1] >> 32)) S.p[i] |= SURV;
+        }
+        else
+        {
+            // first rank of every block of the query's index box, in visiting order (blocks that do not exist hold no rank)
+            u32 nblk = 0;
+            if (lane == 0)
+            {
+                float3 p = make_float3(qx[q], qy[q], qz[q]);
+                if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
+                int a[3], b[3];
+                trees_radius_box(t, p, r, a, b);
+                u32 r0 = 0;
+                for (int x = a[0]; x <= b[0]; x++)
+                    for (int y = a[1]; y <= b[1]; y++)
+                        for (int z = a[2]; z <= b[2]; z++)
+                        {
+                            u32 bid, ecnt;
+                            if (!index_in_range(x, y, z) || !probe_ro(t.btab, t.bmask, pack_key(x, y, z), bid, ecnt)) continue;
+                            if (nblk < nbq) rank0[nblk] = r0, bcnt[nblk] = 0;
+                            r0 += __ldg(&t.bcnt[bid]);
+                            nblk++;
+                        }
+                nblk = min(nblk, nbq);
+            }
+            nblk = __shfl_sync(MMG_FULL, nblk, 0);
+            __syncwarp();
+            // the per-block cut: in ascending (d2, rank) order a hit is taken while its block has handed out fewer than maxPoints
+            // (ranks of one block are consecutive, so the block of a hit is found by searching the blocks' first ranks); of the
+            // taken hits, the last of every run of equal d2 survives
+            u32 pend = 0xFFFFFFFFu, pend_d2 = 0;
             for (u32 base = 0; base < N; base += 32)
             {
                 const u32  i     = base + lane;
                 const bool valid = i < N;
-                const u64  kv    = valid ? key[i] : 0;
+                const u64  kv    = valid ? S.k[i] : 0;
                 u32        ord   = 0xFFFFFFFFu;
                 if (valid)
                 {
@@ -174,19 +292,15 @@ __device__ __forceinline__ void trees_radius_finish(const TreesDev& t, u64* __re
                     while (hi - lo > 1)
                     {
                         const u32 mid = (lo + hi) >> 1;
-                        if (s_rank0[mid] <= rk) lo = mid; else hi = mid;
+                        if (rank0[mid] <= rk) lo = mid; else hi = mid;
                     }
                     ord = lo;
                 }
                 const u32 peers = __match_any_sync(MMG_FULL, ord);
                 bool      acc   = false;
-                if (valid)
-                {
-                    const u32 before = s_cnt[ord] + __popc(peers & ((1u << lane) - 1));
-                    acc              = before < maxp;
-                }
+                if (valid) acc = bcnt[ord] + __popc(peers & ((1u << lane) - 1)) < maxp;
                 __syncwarp();
-                if (valid && lane == __ffs(peers) - 1) s_cnt[ord] += __popc(peers);
+                if (valid && lane == __ffs(peers) - 1) bcnt[ord] += __popc(peers);
                 __syncwarp();
                 const u32 am = __ballot_sync(MMG_FULL, acc);
                 if (am)
@@ -194,65 +308,139 @@ __device__ __forceinline__ void trees_radius_finish(const TreesDev& t, u64* __re
                     const u32 d2  = (u32)(kv >> 32);
                     const int fst = __ffs(am) - 1, lst = 31 - __clz(am);
                     const u32 d2f = __shfl_sync(MMG_FULL, d2, fst);
-                    if (lane == 0 && pend != 0xFFFFFFFFu && pend_d2 != d2f) pos[pend] |= SURV;
+                    if (lane == 0 && pend != 0xFFFFFFFFu && pend_d2 != d2f) S.p[pend] |= SURV;
                     const u32 above = am & ~((2u << lane) - 1u);  // accepted lanes after this one
                     const int nxt   = above ? __ffs(above) - 1 : lane;
                     const u32 d2n   = __shfl_sync(MMG_FULL, d2, nxt);
                     if (acc)
                     {
-                        pos[i] |= ACC;
-                        if (above && d2n != d2) pos[i] |= SURV;
+                        S.p[i] |= ACC;
+                        if (above && d2n != d2) S.p[i] |= SURV;
                     }
                     pend    = base + (u32)lst;
                     pend_d2 = __shfl_sync(MMG_FULL, d2, lst);
                 }
             }
-            if (lane == 0 && pend != 0xFFFFFFFFu) pos[pend] |= SURV;
+            if (lane == 0 && pend != 0xFFFFFFFFu) S.p[pend] |= SURV;
         }
-    }
-    __syncthreads();
-    // ordered compaction of the survivors to the query's place in the result
-    u32 running = 0;
-    for (u32 base = 0; base < N; base += blockDim.x)
-    {
-        const u32  i = base + threadIdx.x;
-        const bool s = i < N && (pos[i] & SURV);
-        const u32  m = __ballot_sync(MMG_FULL, s);
-        if (lane == 0) s_scan[wid] = __popc(m);
-        __syncthreads();
-        u32 before = running, total = running;
-        for (int k = 0; k < nw; k++)
+        __syncwarp();
+        // ordered compaction of the survivors to the query's place in the result
+        const u64    obase = boff[q];
+        const float* gx    = hxyz + 3 * h0;
+        const u32*   gi    = hidx + h0;
+        u32          running = 0;
+        for (u32 base = 0; base < N; base += 32)
         {
-            const u32 c = s_scan[k];
-            if (k < wid) before += c;
-            total += c;
+            const u32  i  = base + lane;
+            const u32  pv = i < N ? S.p[i] : 0u;
+            const bool sv = (pv & SURV) != 0;
+            const u32  m  = __ballot_sync(MMG_FULL, sv);
+            if (sv)
+            {
+                const u64 o = obase + running + __popc(m & ((1u << lane) - 1));
+                const u32 h = pv & IDX;
+                rxyz[3 * o] = gx[3 * (size_t)h], rxyz[3 * o + 1] = gx[3 * (size_t)h + 1], rxyz[3 * o + 2] = gx[3 * (size_t)h + 2];
+                rd2[o] = __uint_as_float((u32)(S.k[i] >> 32));
+                rid[o] = (u64)gi[h];
+            }
+            running += __popc(m);
         }
-        if (s)
-        {
-            const u64 o = obase + before + __popc(m & ((1u << lane) - 1));
-            const u32 h = (u32)(pos[i] & IDX);
-            rxyz[3 * o] = hxyz[3 * (size_t)h], rxyz[3 * o + 1] = hxyz[3 * (size_t)h + 1], rxyz[3 * o + 2] = hxyz[3 * (size_t)h + 2];
-            rd2[o] = __uint_as_float((u32)(key[i] >> 32));
-            rid[o] = (u64)hidx[h];
-        }
-        running = total;
-        __syncthreads();
+        if (lane == 0) outcnt[w] = running;
     }
-    if (threadIdx.x == 0) *outcnt_q = running;
 }
 
-__global__ void __launch_bounds__(TRR_THREADS)
-    k_trees_radius_sort(TreesDev t, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 q0, u32 n, PoseD pose,
-                        int use_pose, float r, u32 maxp, const u32* __restrict__ cnt /*chunk relative*/, const u64* __restrict__ off, u64 off_base,
-                        const u64* __restrict__ key, const float* __restrict__ hxyz, const u32* __restrict__ hidx, u64* __restrict__ gkey, u32* __restrict__ gpos,
-                        u32 gcap /*keys per thread block in gkey / gpos*/, u32 smem_cap,
-                        const u64* __restrict__ boff, float* __restrict__ rxyz, float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt,
-                        u32* __restrict__ next_query)
+// ---------------------------------------------------------------------------------------------------------------------
+// k_trees_radius_sort_block: one thread BLOCK per query, the list in shared memory, for the queries between n_small and
+// n_large hits: many warps sorting lists of thousands of hits each would push the working set (36 bytes per hit) out of
+// L2 (measured: 292 ms for the r = 2 m sweep with warps only, 141 ms with blocks only, profiles/r2h_*). The keys stay where
+// they are loaded; a 16-bit permutation is sorted (stable LSD radix, per-warp histograms of contiguous ranges, one
+// block-wide scan per pass), d2 half first, whole key only when two neighbours tie.
+constexpr int TRB_THREADS = 512, TRB_WARPS = TRB_THREADS / 32;
+constexpr u32 TRB_CAP     = 16384;  // hits per query: 8-byte key + two 2-byte permutation buffers = 192 KB
+__device__ __forceinline__ unsigned short* block_radix_perm(const u64* __restrict__ key, unsigned short* posA, unsigned short* posB, u32 N, u32* hist,
+                                                            u32* s_red /*4*/, u32* s_scan /*TRB_WARPS*/, int first_shift)
 {
+    const int lane = lane_id(), w = threadIdx.x >> 5;
+    const u32 per = (((N + TRB_WARPS - 1) / TRB_WARPS) + 31u) & ~31u, beg = min(N, (u32)w * per), end = min(N, beg + per);
+    if (threadIdx.x < 4) s_red[threadIdx.x] = threadIdx.x < 2 ? 0xFFFFFFFFu : 0u;
+    __syncthreads();
+    {
+        u32 alo = 0xFFFFFFFFu, ahi = 0xFFFFFFFFu, olo = 0, ohi = 0;
+        for (u32 i = threadIdx.x; i < N; i += blockDim.x)
+        {
+            const u64 k = key[i];
+            alo &= (u32)k, ahi &= (u32)(k >> 32), olo |= (u32)k, ohi |= (u32)(k >> 32);
+        }
+        alo = __reduce_and_sync(MMG_FULL, alo), ahi = __reduce_and_sync(MMG_FULL, ahi);
+        olo = __reduce_or_sync(MMG_FULL, olo), ohi = __reduce_or_sync(MMG_FULL, ohi);
+        if (lane == 0) atomicAnd(&s_red[0], alo), atomicAnd(&s_red[1], ahi), atomicOr(&s_red[2], olo), atomicOr(&s_red[3], ohi);
+    }
+    __syncthreads();
+    const u64 diff = ((u64)(s_red[1] ^ s_red[3]) << 32) | (u64)(s_red[0] ^ s_red[2]);
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) posA[i] = (unsigned short)i;
+    __syncthreads();
+    for (int shift = first_shift; shift < 64; shift += 8)
+    {
+        if (((diff >> shift) & 0xFFull) == 0) continue;
+        for (u32 i = threadIdx.x; i < 256u * TRB_WARPS; i += blockDim.x) hist[i] = 0;
+        __syncthreads();
+        for (u32 i = beg + lane; i < end; i += 32) atomicAdd(&hist[(u32)((key[posA[i]] >> shift) & 0xFFull) * TRB_WARPS + w], 1u);
+        __syncthreads();
+        {   // exclusive scan over hist[digit][warp] (4096 entries, 8 consecutive ones per thread)
+            constexpr int E = 256 * TRB_WARPS / TRB_THREADS;
+            u32           v[E], sum = 0;
+#pragma unroll
+            for (int e = 0; e < E; e++) v[e] = hist[threadIdx.x * E + e], sum += v[e];
+            u32 incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
+            {
+                const u32 y = __shfl_up_sync(MMG_FULL, incl, o);
+                if (lane >= o) incl += y;
+            }
+            if (lane == 31) s_scan[w] = incl;
+            __syncthreads();
+            u32 base = incl - sum;
+            for (int k = 0; k < w; k++) base += s_scan[k];
+#pragma unroll
+            for (int e = 0; e < E; e++) hist[threadIdx.x * E + e] = base, base += v[e];
+        }
+        __syncthreads();
+        for (u32 b0 = beg; b0 < end; b0 += 32)
+        {
+            const u32  i     = b0 + lane;
+            const bool valid = i < end;
+            const u32  p     = valid ? posA[i] : 0;
+            const u32  d     = valid ? (u32)((key[p] >> shift) & 0xFFull) : 256u;
+            const u32  peers = __match_any_sync(MMG_FULL, d);  // (eight ballots instead: 25 % slower, profiles/r2h_*)
+            if (valid) posB[hist[d * TRB_WARPS + w] + __popc(peers & ((1u << lane) - 1u))] = (unsigned short)p;
+            __syncwarp();
+            if (valid && lane == __ffs(peers) - 1) hist[d * TRB_WARPS + w] += __popc(peers);
+            __syncwarp();
+        }
+        __syncthreads();
+        unsigned short* t = posA;
+        posA              = posB;
+        posB              = t;
+    }
+    return posA;
+}
+
+__global__ void __launch_bounds__(TRB_THREADS)
+    k_trees_radius_sort_block(TreesDev t, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 q0, u32 n,
+                              PoseD pose, int use_pose, float r, u32 maxp, const u32* __restrict__ cnt, const u64* __restrict__ off, u64 off_base,
+                              const u64* __restrict__ key, const float* __restrict__ hxyz, const u32* __restrict__ hidx, const u64* __restrict__ boff,
+                              float* __restrict__ rxyz, float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt,
+                              u32* __restrict__ next_query, u32 n_small, u32 n_large)
+{
+    constexpr unsigned short ACC = 1u << 15, SURV = 1u << 14, IDX = SURV - 1u;
     extern __shared__ __align__(16) unsigned char smem[];
-    u64*            skey = reinterpret_cast<u64*>(smem);
-    unsigned short* spos = reinterpret_cast<unsigned short*>(smem + (size_t)smem_cap * 8);
-    __shared__ u32  s_rank0[TRR_NBQ_MAX + 1], s_cnt[TRR_NBQ_MAX], s_scan[TRR_THREADS / 32], s_q, s_nblk;
+    u64*            skey  = reinterpret_cast<u64*>(smem);
+    unsigned short* spos  = reinterpret_cast<unsigned short*>(smem + (size_t)n_large * 8);
+    unsigned short* spos2 = spos + n_large;
+    __shared__ u32  s_rank0[TRR_NBQ_MAX + 1], s_cnt[TRR_NBQ_MAX], s_scan[TRB_WARPS], s_q, s_nblk, s_red[4], s_flag;
+    __shared__ u32  s_hist[256 * TRB_WARPS];
+    const int       lane = lane_id(), wid = threadIdx.x >> 5;
     for (;;)
     {
         __syncthreads();
@@ -261,14 +449,10 @@ __global__ void __launch_bounds__(TRR_THREADS)
         const u32 w = s_q;
         if (w >= n) break;
         const u32 q = q0 + w, N = cnt[w];
-        if (N == 0)
-        {
-            if (threadIdx.x == 0) outcnt[w] = 0;
-            continue;
-        }
+        if (N <= n_small || N > n_large) continue;
         const u64 h0 = off[q] - off_base;
         if (maxp != 0 && threadIdx.x == 0)
-        {   // first rank of every block of the query's index box, in visiting order (blocks that do not exist hold no rank)
+        {   // first rank of every block of the query's index box, in visiting order
             float3 p = make_float3(qx[q], qy[q], qz[q]);
             if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
             int a[3], b[3];
@@ -286,33 +470,105 @@ __global__ void __launch_bounds__(TRR_THREADS)
                     }
             s_nblk = min(nb, TRR_NBQ_MAX);
         }
-        u32 P = 1;
-        while (P < N) P <<= 1;
-        if (P <= smem_cap)
+        for (u32 i = threadIdx.x; i < N; i += blockDim.x) skey[i] = key[h0 + i];
+        __syncthreads();
+        unsigned short* sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, 32);
+        if (threadIdx.x == 0) s_flag = 0;
+        __syncthreads();
         {
-            for (u32 i = threadIdx.x; i < P; i += blockDim.x)
-            {
-                skey[i] = i < N ? key[h0 + i] : ~0ull;
-                spos[i] = (unsigned short)(i < N ? i : 0);
-            }
-            __syncthreads();
-            block_bitonic<unsigned short>(skey, spos, P);
-            trees_radius_finish<unsigned short, 16>(t, skey, spos, N, maxp, s_rank0, s_cnt, s_nblk, hxyz + 3 * h0, hidx + h0, boff[q], rxyz, rd2, rid,
-                                                    outcnt + w, s_scan);
+            bool tie = false;
+            for (u32 i = threadIdx.x; i + 1 < N; i += blockDim.x) tie |= (u32)(skey[sp[i]] >> 32) == (u32)(skey[sp[i + 1]] >> 32);
+            if (tie) s_flag = 1;
         }
-        else
-        {   // larger than shared memory: the same steps over this thread block's own slice of global scratch
-            u64* gk = gkey + (size_t)blockIdx.x * gcap;
-            u32* gp = gpos + (size_t)blockIdx.x * gcap;
-            for (u32 i = threadIdx.x; i < P; i += blockDim.x)
-            {
-                gk[i] = i < N ? key[h0 + i] : ~0ull;
-                gp[i] = i < N ? i : 0;
-            }
-            __syncthreads();
-            block_bitonic<u32>(gk, gp, P);
-            trees_radius_finish<u32, 32>(t, gk, gp, N, maxp, s_rank0, s_cnt, s_nblk, hxyz + 3 * h0, hidx + h0, boff[q], rxyz, rd2, rid, outcnt + w, s_scan);
+        __syncthreads();
+        if (s_flag) sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, 0);
+        auto K = [&](u32 i) -> u64 { return skey[sp[i] & IDX]; };
+        if (maxp == 0)
+        {   // (the flags of position i + 1 may be written while position i reads it: they sit above the index bits K() masks off)
+            for (u32 i = threadIdx.x; i < N; i += blockDim.x)
+                if (i + 1 >= N || (u32)(K(i) >> 32) != (u32)(K(i + 1) >> 32)) sp[i] |= SURV;
         }
+        else if (wid == 0)
+        {
+            const u32 nblk = s_nblk;
+            u32       pend = 0xFFFFFFFFu, pend_d2 = 0;
+            for (u32 base = 0; base < N; base += 32)
+            {
+                const u32  i     = base + lane;
+                const bool valid = i < N;
+                const u64  kv    = valid ? K(i) : 0;
+                u32        ord   = 0xFFFFFFFFu;
+                if (valid)
+                {
+                    const u32 rk = (u32)kv;
+                    u32       lo = 0, hi = nblk;
+                    while (hi - lo > 1)
+                    {
+                        const u32 mid = (lo + hi) >> 1;
+                        if (s_rank0[mid] <= rk) lo = mid; else hi = mid;
+                    }
+                    ord = lo;
+                }
+                const u32 peers = __match_any_sync(MMG_FULL, ord);
+                bool      acc   = false;
+                if (valid) acc = s_cnt[ord] + __popc(peers & ((1u << lane) - 1)) < maxp;
+                __syncwarp();
+                if (valid && lane == __ffs(peers) - 1) s_cnt[ord] += __popc(peers);
+                __syncwarp();
+                const u32 am = __ballot_sync(MMG_FULL, acc);
+                if (am)
+                {
+                    const u32 d2  = (u32)(kv >> 32);
+                    const int fst = __ffs(am) - 1, lst = 31 - __clz(am);
+                    const u32 d2f = __shfl_sync(MMG_FULL, d2, fst);
+                    if (lane == 0 && pend != 0xFFFFFFFFu && pend_d2 != d2f) sp[pend] |= SURV;
+                    const u32 above = am & ~((2u << lane) - 1u);
+                    const int nxt   = above ? __ffs(above) - 1 : lane;
+                    const u32 d2n   = __shfl_sync(MMG_FULL, d2, nxt);
+                    if (acc)
+                    {
+                        sp[i] |= ACC;
+                        if (above && d2n != d2) sp[i] |= SURV;
+                    }
+                    pend    = base + (u32)lst;
+                    pend_d2 = __shfl_sync(MMG_FULL, d2, lst);
+                }
+            }
+            if (lane == 0 && pend != 0xFFFFFFFFu) sp[pend] |= SURV;
+        }
+        __syncthreads();
+        // ordered compaction of the survivors to the query's place in the result
+        const u64    obase = boff[q];
+        const float* gx    = hxyz + 3 * h0;
+        const u32*   gi    = hidx + h0;
+        u32          running = 0;
+        for (u32 base = 0; base < N; base += blockDim.x)
+        {
+            const u32  i  = base + threadIdx.x;
+            const u32  pv = i < N ? sp[i] : 0u;
+            const bool sv = (pv & SURV) != 0;
+            const u32  m  = __ballot_sync(MMG_FULL, sv);
+            if (lane == 0) s_scan[wid] = __popc(m);
+            __syncthreads();
+            u32 before = running, total = running;
+            for (int k = 0; k < TRB_WARPS; k++)
+            {
+                const u32 c = s_scan[k];
+                if (k < wid) before += c;
+                total += c;
+            }
+            if (sv)
+            {
+                const u64 o = obase + before + __popc(m & ((1u << lane) - 1));
+                const u32 h = pv & IDX;
+                rxyz[3 * o] = gx[3 * (size_t)h], rxyz[3 * o + 1] = gx[3 * (size_t)h + 1], rxyz[3 * o + 2] = gx[3 * (size_t)h + 2];
+                rd2[o] = __uint_as_float((u32)(skey[h] >> 32));
+                rid[o] = (u64)gi[h];
+            }
+            running = total;
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) outcnt[w] = running;
     }
 }
 
