@@ -39,6 +39,16 @@
  *     for identity; points are composed in double and rounded to float exactly as
  *     mrpt::poses::CPose3D::composePoint does.
  *   - there is no CPU fallback: without a CUDA device mmg_create fails.
+ *   - threading: the const queries (mmg_nn_*_batch, mmg_match*_batch, mmg_likelihood, mmg_export, mmg_voxel_stats,
+ *     mmg_num_points) may run on ONE map from several host threads and streams at once, like the reference's
+ *     (SparseTreesPointCloud.h:164-209,449): every call takes its scratch from the stream-ordered memory pool, and the
+ *     hits of mmg_nn_radius_batch belong to the calling thread until its mmg_nn_radius_fetch. MMG_MEM_HOST calls with
+ *     pageable buffers serialise on a per-map mutex. Inserts, clear, set_params, bcast are single-writer: no other call
+ *     may touch the map meanwhile.
+ *   - a MMG_MEM_DEVICE insert without a min-distance test returns once its kernels are enqueued on `stream`; the
+ *     counters it produces are collected by the next call on the map that needs them, and points of such a batch whose
+ *     voxel index is out of range are reported (MMG_ERR_OUT_OF_RANGE) by that later call. Work on OTHER streams that
+ *     reads the map must be ordered after the insert's stream by the caller.
  */
 #ifndef MOLA_B200_MMG_H
 #define MOLA_B200_MMG_H
@@ -223,8 +233,9 @@ int mmg_comm_init(const uint8_t id[128], int rank, int nranks, int device, mmg_c
 int mmg_comm_destroy(mmg_comm* c);
 int mmg_bcast(mmg_map* m, mmg_comm* c, int root, void* stream);
 
-/* Diagnostics: process-wide A/B switches for the profiles ("nn_kernel", "nn_gw", "nn_minb", "nn_permute"); results are
- * identical for every setting, only the kernel organisation changes. */
+/* Diagnostics: process-wide A/B switches for the profiles ("nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute",
+ * "radius_chunk_hits", "sv_split_hits", "nn_task_minb", "radius_warp_max"; also MMG_TUNE="knob=value,..." in the
+ * environment). Results are identical for every setting, only the kernel organisation changes. */
 int mmg_set_tuning(const char* key, int value);
 
 /* Number of kernels this library has launched in the calling process. */

@@ -7,7 +7,6 @@
 #include "mmg_trees_radius.cuh"
 
 #include <cmath>
-#include <cstdio>
 #include <cstring>
 
 using namespace mmg;
@@ -546,12 +545,6 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
                     MMG_LAUNCH(k_trees_radius_sort_block, (unsigned)std::min<size_t>(k, (size_t)m->num_sms * bpsm), TRB_THREADS, smem, st, s->dev, dx, dy, dz,
                                (u32)a, (u32)k, T, pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey,
                                (const float*)hxyz, (const u32*)hidx, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next + 1, n_small, n_large);
-                    if (getenv("MMG_DEBUG"))
-                    {
-                        cudaError_t e = cudaStreamSynchronize(st);
-                        fprintf(stderr, "[trees_radius] maxcnt %u n_small %u n_large %u smem %zu bpsm %u -> %s / %s\n", herr.maxcnt, n_small, n_large, smem, bpsm,
-                                cudaGetErrorString(e), cudaGetErrorString(cudaGetLastError()));
-                    }
                 }
             }
             exclusive_scan<u32, u64>(outcnt, noff, n, noff + n, noff + n + 1, st);

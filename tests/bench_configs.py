@@ -150,7 +150,7 @@ def run_c3(ctx):
     gm, gcov = g.voxelStats()
     stats_s = time.perf_counter() - t0
     # CPU twin (port: the k-NN / covariance extension has no reference behaviour)
-    o = mmo.OracleMap(1, 0.2)
+    o = mmo.OracleMap(1, 0.2, which="port")  # k-NN extension: port only (the reference throws)
     o.enable_knn_extension()
     t0 = time.perf_counter()
     for s in scans:

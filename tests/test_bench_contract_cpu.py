@@ -31,3 +31,20 @@ def test_reference_arm_other_ranks_exit_quietly(built):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0"],
                        capture_output=True, text=True, timeout=120, cwd=ROOT, env=env)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_config_object_is_the_same_in_both_arms_and_stamp_is_stable(built):
+    """`config` comes from one function for both arms (the driver compares them), and the source stamp that guards
+    profiles/traffic.json is a pure function of the kernel sources."""
+    sys.path.insert(0, ROOT)
+    import bench
+    a = bench.make_config(10165305, 389152, 496, 1_000_000)
+    b = bench.make_config(10165305, 389152, 496, 1_000_000)
+    assert a == b and set(a) == {"workload", "map_points", "map_voxels", "map_scans", "queries_per_step_per_gpu", "l2"}
+    s1, s2 = bench.source_stamp(), bench.source_stamp()
+    assert s1 == s2 and len(s1) == 16
+    tj = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tj):
+        t = json.load(open(tj))
+        if "labels" in t:  # a capture of another tree is allowed to exist, bench.py then refuses to quote it
+            assert "source_stamp" in t and "nn_single_step" in t["labels"]

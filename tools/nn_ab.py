@@ -81,6 +81,36 @@ def main():
             torch.cuda.synchronize()
             st = {"e2e_ms": 1e3 * (time.perf_counter() - t0) / steps, "e2e_same": bool(all(
                 np.array_equal(a.numpy().view(np.uint8), b.cpu().numpy().view(np.uint8)) for a, b in zip(ho, out)))}
+        if os.environ.get("AB_MATCH"):
+            # mmg_match_batch (threshold 0.5 m) on the same batch, device buffers: rate relative to nn_single, pairings checked
+            thr2 = 0.25
+            midx = torch.zeros(n, dtype=torch.int32, device=dev)
+            mxyz = torch.zeros((n, 3), dtype=torch.float32, device=dev)
+            md2 = torch.zeros(n, dtype=torch.float32, device=dev)
+            mid = torch.zeros(n, dtype=torch.int64, device=dev)
+            cnt = C.c_uint64()
+
+            def step_match():
+                capi.check(lib.mmg_match_batch(gmap._h, fp(dq[0]), fp(dq[1]), fp(dq[2]), C.c_size_t(n), None, C.c_float(thr2), C.byref(cnt),
+                                               vp(midx), vp(mxyz), vp(md2), vp(mid), capi.MEM_DEVICE, sp))
+            for _ in range(3):
+                flush.zero_()
+                step_match()
+            mm = []
+            for _ in range(steps):
+                flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                step_match()
+                e1.record(stream)
+                e1.synchronize()
+                mm.append(e0.elapsed_time(e1))
+            k = int(cnt.value)
+            keep = (out[0] > 0) & (out[2] < thr2)
+            ok = bool(k == int(keep.sum().item()) and torch.equal(midx[:k].long(), torch.nonzero(keep).flatten()) and
+                      torch.equal(mid[:k], out[3][keep]) and torch.equal(md2[:k], out[2][keep]))
+            st = dict(st or {}, match_ms=float(np.mean(mm)), match_pairings=k, match_equals_filtered_nn_single=ok,
+                      match_rate_vs_nn_single=float(np.mean(ms) / np.mean(mm)))
         res = [o.cpu().numpy() for o in out]
         same = None
         if ref is None:

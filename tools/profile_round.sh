@@ -1,15 +1,21 @@
 #!/bin/bash
 # One gpurun call's worth of round-end evidence (run from the repo root on a B200 box):
-#   bash tools/profile_round.sh <tag>     ->  gpurun_out/<tag>_*  (copy what should be judged into profiles/)
+#   bash tools/profile_round.sh <tag> [full]    ->  gpurun_out/<tag>_*
+# Afterwards, in the build container (ncu reads the reports without a GPU):
+#   ncu -i gpurun_out/<tag>_prof_nn.ncu-rep --page raw --csv > profiles/<tag>_ncu_full_nn_single_step.csv     (etc.)
+#   python tools/ncu_summary.py nn_single_step=profiles/<tag>_ncu_full_nn_single_step.csv ... > profiles/traffic.json
+# traffic.json carries a hash of the kernel sources; bench.py quotes it only while the sources are the same.
 set -x
 T=${1:-rX}
-python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest_gpu.log 2>&1; tail -2 gpurun_out/${T}_pytest_gpu.log
+python -m pytest tests -m gpu -q > gpurun_out/${T}_pytest_gpu.log 2>&1; tail -2 gpurun_out/${T}_pytest_gpu.log
+python bench.py --impl reference --steps 20 --warmup 3 > gpurun_out/${T}_bench_reference_n1.json 2> gpurun_out/${T}_bench_reference_n1.err
 python bench.py --steps 20 --warmup 3 > gpurun_out/${T}_bench_n1.json 2> gpurun_out/${T}_bench_n1.err
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_bench_reference_n1.json 2> gpurun_out/${T}_bench_reference_n1.err
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/${T}_launches_bench_steps3.csv python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/${T}_ncu1.log 2>&1
 if [ "$2" = "full" ]; then
-ncu --set full --clock-control none --import-source on -k regex:k_nn_single_pruned -s 5 -c 1 -o gpurun_out/${T}_prof_nn python bench.py --steps 3 --warmup 3 --no-cpu --insert-scans 0 > gpurun_out/${T}_ncu2.log 2>&1
+# the three kernels of one nn_single step (launches 10-12 of tools/nn_ab.py: after the warm-up steps)
+AB_STEPS=3 ncu --set full --clock-control none --import-source on -k regex:k_nn_ -s 9 -c 3 -o gpurun_out/${T}_prof_nn python tools/nn_ab.py nn_kernel=0 > gpurun_out/${T}_ncu2.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_insert_rank -s 2 -c 2 -o gpurun_out/${T}_prof_rank python bench.py --only insert_batched > gpurun_out/${T}_ncu3.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_insert_commit -s 2 -c 1 -o gpurun_out/${T}_prof_commit python bench.py --only insert_batched > gpurun_out/${T}_ncu4.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_insert_commit -s 2 -c 2 -o gpurun_out/${T}_prof_commit python bench.py --only insert_batched > gpurun_out/${T}_ncu4.log 2>&1
+compute-sanitizer --tool racecheck --print-limit 20 python tools/racecheck_insert.py > gpurun_out/${T}_racecheck_insert.log 2>&1; tail -5 gpurun_out/${T}_racecheck_insert.log
 fi
 cut -c1-300 gpurun_out/${T}_bench_n1.json
