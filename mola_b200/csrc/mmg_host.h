@@ -152,6 +152,8 @@ enum Tune
     T_SV_SPLIT_HITS,      // SparseVoxel radius search: hits one pass may index (2^31 - 1); smaller values exercise the splitting
     T_NN_TASK_MINB,       // k_nn_tasks: resident blocks of 256 per SM it is compiled for (5 | 6 | 8)
     T_RADIUS_WARP_MAX,    // SparseTrees radius search: lists up to this many hits are sorted by a warp, longer ones by a block
+    T_RADIUS_BLOCK_MID,   // SparseTrees radius search: lists up to this many hits share an SM three blocks at a time
+    T_RADIUS_Q16,         // SparseTrees radius search: sort on the 16-bit monotone image of d2 (1) or on the raw key bits (0)
     T_COUNT
 };
 extern int g_tune[T_COUNT];

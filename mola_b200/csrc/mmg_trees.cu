@@ -454,7 +454,7 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     if (!cnt || !off || !boff) return MMG_ERR_OUT_OF_MEM;
     u32*            bound = cnt + n + 1;
     u32*            next  = (u32*)(bound + n + 1);
-    TreesRadiusErr* derr  = (TreesRadiusErr*)(next + 2);
+    TreesRadiusErr* derr  = (TreesRadiusErr*)(next + 4);
     u64*            noff  = boff + (n + 2 + ns);
     MMG_CUDA(cudaMemsetAsync(off, 0, (n + 1) * sizeof(u64), st));
     u64 H = 0, B = 0;
@@ -462,7 +462,7 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     {
         const PoseD    T  = make_pose(pose12);
         const unsigned nb = persistent_blocks(m, n, 8, 8);
-        MMG_CUDA(cudaMemsetAsync(next, 0, 2 * sizeof(u32) + sizeof(TreesRadiusErr), st));
+        MMG_CUDA(cudaMemsetAsync(next, 0, 4 * sizeof(u32) + sizeof(TreesRadiusErr), st));
         MMG_LAUNCH((k_trees_radius_hits<0>), nb, 256, 0, st, s->dev, dx, dy, dz, 0u, (u32)n, T, pose12 ? 1 : 0, r2, r, cnt, (const u64*)nullptr, 0ull,
                    (u64*)nullptr, (float*)nullptr, (u32*)nullptr, derr);
         // the place reserved for a query: all its hits, or at most maxPoints per block of its index box
@@ -524,14 +524,15 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
                 }
                 MMG_LAUNCH((k_trees_radius_hits<1>), persistent_blocks(m, k, 8, 8), 256, 0, st, s->dev, dx, dy, dz, (u32)a, (u32)k, T, pose12 ? 1 : 0, r2, r,
                            (u32*)nullptr, (const u64*)off, hoff[a], hkey, hxyz, hidx, derr);
-                MMG_CUDA(cudaMemsetAsync(next, 0, 2 * sizeof(u32), st));
+                MMG_CUDA(cudaMemsetAsync(next, 0, 3 * sizeof(u32), st));
                 // short lists: a warp per query over L2-resident scratch; long ones: a block per query in shared memory
-                const u32 n_small = (u32)std::max(0, g_tune[T_RADIUS_WARP_MAX]);
+                const u32   n_small = (u32)std::max(0, g_tune[T_RADIUS_WARP_MAX]);
+                const float qscale  = (r2 > 1e-30f && r2 < 1e30f && g_tune[T_RADIUS_Q16]) ? 65536.0f / r2 : 0.f;
                 const u32 n_large = herr.maxcnt > n_small ? std::min<u32>(TRB_CAP, (herr.maxcnt + 1023u) & ~1023u) : n_small;
                 MMG_LAUNCH(k_trees_radius_sort, (unsigned)std::min<size_t>((k + TRR_WARPS - 1) / TRR_WARPS, sblocks), TRR_THREADS, 0, st, s->dev, dx, dy, dz,
                            (u32)a, (u32)k, T, pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey,
                            (const float*)hxyz, (const u32*)hidx, bufk, bufp, hmax, gtab, nbq32, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next, n_small,
-                           n_large);
+                           n_large, qscale);
                 if (n_large > n_small)
                 {
                     static bool attr_set = false;
@@ -540,11 +541,19 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
                         MMG_CUDA(cudaFuncSetAttribute(k_trees_radius_sort_block, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TRB_CAP * 12)));
                         attr_set = true;
                     }
-                    const size_t   smem = (size_t)n_large * 12;
-                    const unsigned bpsm = (unsigned)std::max<size_t>(1, std::min<size_t>(4, (220 * 1024) / (smem + 26 * 1024)));
-                    MMG_LAUNCH(k_trees_radius_sort_block, (unsigned)std::min<size_t>(k, (size_t)m->num_sms * bpsm), TRB_THREADS, smem, st, s->dev, dx, dy, dz,
-                               (u32)a, (u32)k, T, pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey,
-                               (const float*)hxyz, (const u32*)hidx, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next + 1, n_small, n_large);
+                    // two size classes, so that the many medium lists do not pay the shared memory of the few long ones:
+                    // up to 6144 hits three blocks share an SM, above that one block has it alone
+                    const u32 mid = std::min<u32>(n_large, (u32)std::max(0, g_tune[T_RADIUS_BLOCK_MID]));
+                    const u32 lo[2] = {n_small, std::max(mid, n_small)}, hi[2] = {std::max(mid, n_small), n_large};
+                    for (int c = 0; c < 2; c++)
+                    {
+                        if (hi[c] <= lo[c]) continue;
+                        const size_t   smem = (size_t)hi[c] * 12;
+                        const unsigned bpsm = (unsigned)std::max<size_t>(1, std::min<size_t>(4, (220 * 1024) / (smem + 26 * 1024)));
+                        MMG_LAUNCH(k_trees_radius_sort_block, (unsigned)std::min<size_t>(k, (size_t)m->num_sms * bpsm), TRB_THREADS, smem, st, s->dev, dx, dy,
+                                   dz, (u32)a, (u32)k, T, pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey,
+                                   (const float*)hxyz, (const u32*)hidx, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next + 1 + c, lo[c], hi[c], qscale);
+                    }
                 }
             }
             exclusive_scan<u32, u64>(outcnt, noff, n, noff + n, noff + n + 1, st);

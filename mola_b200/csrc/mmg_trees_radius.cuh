@@ -123,19 +123,28 @@ static __global__ void k_trees_radius_bound(const u32* __restrict__ cnt, u32 n, 
 // insertion order. Per pass: digit histogram in the warp's 1 KB of shared memory, exclusive scan by the warp, scatter 32
 // pairs at a time, equal digits of a group ranked with __match_any_sync.
 constexpr int TRR_WARPS = TRR_THREADS / 32;
+// Sort digits. Every hit has d2 < r2, so q16 = floor(d2 * 65536 / r2) is a MONOTONE 16-bit image of the distance: two radix
+// passes on q16 order the list up to the (few, short) runs of hits that share a q16, and those runs are put in exact
+// (d2, rank) order by an insertion sort on the full 64-bit key, ties included. Half the passes of sorting the 32 d2 bits.
+// qscale = 0 selects the raw key bits (lists with a run of more than 64 equal q16, e.g. thousands of duplicated points).
+__device__ __forceinline__ u32 trr_q16(u64 key, float qscale) { return min(65535u, (u32)(__uint_as_float((u32)(key >> 32)) * qscale)); }
+__device__ __forceinline__ u32 trr_digit(u64 key, int shift, float qscale)
+{
+    return qscale > 0.f ? (trr_q16(key, qscale) >> shift) & 0xFFu : (u32)((key >> shift) & 0xFFull);
+}
 struct HitBuf
 {
     u64* k;
     u32* p;
 };
 __device__ __forceinline__ void warp_radix_pass(const u64* __restrict__ sk, const u32* __restrict__ sp /*nullable: identity*/, HitBuf dst, u32 N, int shift,
-                                                u32* hist)
+                                                u32* hist, float qscale)
 {
     const int lane = lane_id();
 #pragma unroll
     for (int e = 0; e < 8; e++) hist[lane * 8 + e] = 0;
     __syncwarp();
-    for (u32 i = lane; i < N; i += 32) atomicAdd(&hist[(u32)((sk[i] >> shift) & 0xFFull)], 1u);
+    for (u32 i = lane; i < N; i += 32) atomicAdd(&hist[trr_digit(sk[i], shift, qscale)], 1u);
     __syncwarp();
     {
         u32 v[8], sum = 0;
@@ -159,7 +168,7 @@ __device__ __forceinline__ void warp_radix_pass(const u64* __restrict__ sk, cons
         const bool valid = i < N;
         const u64  k     = valid ? sk[i] : 0ull;
         const u32  p     = valid ? (sp ? sp[i] : i) : 0u;
-        const u32  d     = valid ? (u32)((k >> shift) & 0xFFull) : 256u;
+        const u32  d     = valid ? trr_digit(k, shift, qscale) : 256u;
         const u32  peers = __match_any_sync(MMG_FULL, d);
         if (valid)
         {
@@ -172,11 +181,50 @@ __device__ __forceinline__ void warp_radix_pass(const u64* __restrict__ sk, cons
         __syncwarp();
     }
 }
-// sorts the N pairs (key[i], i) on the key bits [first_shift, 64); returns the buffer that holds the result
-__device__ __forceinline__ HitBuf warp_radix_sort(const u64* __restrict__ key, HitBuf A, HitBuf B, u32 N, int first_shift, u32* hist)
+// sorts the N pairs (key[i], i) by key; returns the buffer that holds the result
+__device__ __forceinline__ HitBuf warp_radix_sort(const u64* __restrict__ key, HitBuf A, HitBuf B, u32 N, float qscale, u32* hist)
 {
-    const int lane = lane_id();
-    u64       a = ~0ull, o = 0ull;
+    const int  lane = lane_id();
+    const u64* sk   = key;
+    const u32* sp   = nullptr;
+    HitBuf     dst = A, other = B;
+    if (qscale > 0.f)
+    {
+        for (int shift = 0; shift < 16; shift += 8)
+        {
+            warp_radix_pass(sk, sp, dst, N, shift, hist, qscale);
+            sk = dst.k, sp = dst.p;
+            const HitBuf t = dst;
+            dst            = other;
+            other          = t;
+        }
+        __syncwarp();
+        // exact order inside the runs of equal q16 (each run is handled by the lane that meets its head)
+        bool long_run = false;
+        for (u32 i = lane; i < N; i += 32)
+        {
+            const u32 qi = trr_q16(other.k[i], qscale);
+            if ((i == 0 || trr_q16(other.k[i - 1], qscale) != qi) && i + 1 < N && trr_q16(other.k[i + 1], qscale) == qi)
+            {
+                u32 e = i + 2;
+                while (e < N && trr_q16(other.k[e], qscale) == qi) e++;
+                if (e - i > 64) long_run = true;
+                else
+                    for (u32 a = i + 1; a < e; a++)
+                    {
+                        const u64 ka = other.k[a];
+                        const u32 pa = other.p[a];
+                        u32       b  = a;
+                        for (; b > i && other.k[b - 1] > ka; b--) other.k[b] = other.k[b - 1], other.p[b] = other.p[b - 1];
+                        other.k[b] = ka, other.p[b] = pa;
+                    }
+            }
+        }
+        __syncwarp();
+        if (!__any_sync(MMG_FULL, long_run)) return other;
+        sk = key, sp = nullptr, dst = A, other = B;  // start over on the raw bits
+    }
+    u64 a = ~0ull, o = 0ull;
     for (u32 i = lane; i < N; i += 32)
     {
         const u64 k = key[i];
@@ -185,20 +233,17 @@ __device__ __forceinline__ HitBuf warp_radix_sort(const u64* __restrict__ key, H
     const u32 dlo = __reduce_and_sync(MMG_FULL, (u32)a) ^ __reduce_or_sync(MMG_FULL, (u32)o);
     const u32 dhi = __reduce_and_sync(MMG_FULL, (u32)(a >> 32)) ^ __reduce_or_sync(MMG_FULL, (u32)(o >> 32));
     const u64 diff = ((u64)dhi << 32) | (u64)dlo;
-    const u64* sk  = key;
-    const u32* sp  = nullptr;
-    HitBuf     dst = A, other = B;
-    for (int shift = first_shift; shift < 64; shift += 8)
+    for (int shift = 0; shift < 64; shift += 8)
     {
         if (((diff >> shift) & 0xFFull) == 0) continue;
-        warp_radix_pass(sk, sp, dst, N, shift, hist);
+        warp_radix_pass(sk, sp, dst, N, shift, hist, 0.f);
         sk = dst.k, sp = dst.p;
         const HitBuf t = dst;
         dst            = other;
         other          = t;
     }
     if (!sp)
-    {   // no digit varied (one hit, or all keys equal on these bits): the input order is the sorted order
+    {   // no digit varied (one hit, or all keys equal): the input order is the sorted order
         for (u32 i = lane; i < N; i += 32) A.k[i] = key[i], A.p[i] = i;
         __syncwarp();
         return A;
@@ -212,7 +257,7 @@ __global__ void __launch_bounds__(TRR_THREADS)
                         const u64* __restrict__ key, const float* __restrict__ hxyz, const u32* __restrict__ hidx, u64* __restrict__ bufk,
                         u32* __restrict__ bufp, u64 hc /*hits of the chunk: bufk / bufp hold two buffers of that length*/, u32* __restrict__ gtab,
                         u32 nbq /*gtab: 2 * nbq words per warp of the grid*/, const u64* __restrict__ boff, float* __restrict__ rxyz,
-                        float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt, u32* __restrict__ next_query, u32 n_small, u32 n_large)
+                        float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt, u32* __restrict__ next_query, u32 n_small, u32 n_large, float qscale)
 {
     // this kernel takes the queries with at most n_small hits (their lists stay in L2 however many warps run) and those with
     // more than n_large (too long for the block kernel's shared memory); k_trees_radius_sort_block takes the ones in between
@@ -237,14 +282,8 @@ __global__ void __launch_bounds__(TRR_THREADS)
         if (N > n_small && N <= n_large) continue;
         const u64    h0 = off[q] - off_base;
         const HitBuf A{bufk + h0, bufp + h0}, B{bufk + hc + h0, bufp + hc + h0};
-        HitBuf       S = warp_radix_sort(key + h0, A, B, N, 32, hist);
+        HitBuf       S = warp_radix_sort(key + h0, A, B, N, qscale, hist);
         __syncwarp();
-        {
-            bool tie = false;
-            for (u32 i = lane; i + 1 < N; i += 32) tie |= (u32)(S.k[i] >> 32) == (u32)(S.k[i + 1] >> 32);
-            if (__any_sync(MMG_FULL, tie)) S = warp_radix_sort(key + h0, A, B, N, 0, hist);
-            __syncwarp();
-        }
         if (maxp == 0)
         {   // every hit enters the map: the last of each run of equal d2 survives
             for (u32 i = lane; i < N; i += 32)
@@ -354,12 +393,13 @@ __global__ void __launch_bounds__(TRR_THREADS)
 // n_large hits: many warps sorting lists of thousands of hits each would push the working set (36 bytes per hit) out of
 // L2 (measured: 292 ms for the r = 2 m sweep with warps only, 141 ms with blocks only, profiles/r2h_*). The keys stay where
 // they are loaded; a 16-bit permutation is sorted (stable LSD radix, per-warp histograms of contiguous ranges, one
-// block-wide scan per pass), d2 half first, whole key only when two neighbours tie.
+// block-wide scan per pass) on the 16-bit image of d2, then the short runs of equal image are put in exact key order.
 constexpr int TRB_THREADS = 512, TRB_WARPS = TRB_THREADS / 32;
 constexpr u32 TRB_CAP     = 16384;  // hits per query: 8-byte key + two 2-byte permutation buffers = 192 KB
 __device__ __forceinline__ unsigned short* block_radix_perm(const u64* __restrict__ key, unsigned short* posA, unsigned short* posB, u32 N, u32* hist,
-                                                            u32* s_red /*4*/, u32* s_scan /*TRB_WARPS*/, int first_shift)
+                                                            u32* s_red /*4*/, u32* s_scan /*TRB_WARPS*/, float qscale)
 {
+    // qscale > 0: two passes on the 16-bit monotone image of d2 (trr_q16); else every varying byte of the raw 64-bit key
     const int lane = lane_id(), w = threadIdx.x >> 5;
     const u32 per = (((N + TRB_WARPS - 1) / TRB_WARPS) + 31u) & ~31u, beg = min(N, (u32)w * per), end = min(N, beg + per);
     if (threadIdx.x < 4) s_red[threadIdx.x] = threadIdx.x < 2 ? 0xFFFFFFFFu : 0u;
@@ -379,12 +419,12 @@ __device__ __forceinline__ unsigned short* block_radix_perm(const u64* __restric
     const u64 diff = ((u64)(s_red[1] ^ s_red[3]) << 32) | (u64)(s_red[0] ^ s_red[2]);
     for (u32 i = threadIdx.x; i < N; i += blockDim.x) posA[i] = (unsigned short)i;
     __syncthreads();
-    for (int shift = first_shift; shift < 64; shift += 8)
+    for (int shift = 0; shift < (qscale > 0.f ? 16 : 64); shift += 8)
     {
-        if (((diff >> shift) & 0xFFull) == 0) continue;
+        if (!(qscale > 0.f) && ((diff >> shift) & 0xFFull) == 0) continue;
         for (u32 i = threadIdx.x; i < 256u * TRB_WARPS; i += blockDim.x) hist[i] = 0;
         __syncthreads();
-        for (u32 i = beg + lane; i < end; i += 32) atomicAdd(&hist[(u32)((key[posA[i]] >> shift) & 0xFFull) * TRB_WARPS + w], 1u);
+        for (u32 i = beg + lane; i < end; i += 32) atomicAdd(&hist[trr_digit(key[posA[i]], shift, qscale) * TRB_WARPS + w], 1u);
         __syncthreads();
         {   // exclusive scan over hist[digit][warp] (4096 entries, 8 consecutive ones per thread)
             constexpr int E = 256 * TRB_WARPS / TRB_THREADS;
@@ -411,7 +451,7 @@ __device__ __forceinline__ unsigned short* block_radix_perm(const u64* __restric
             const u32  i     = b0 + lane;
             const bool valid = i < end;
             const u32  p     = valid ? posA[i] : 0;
-            const u32  d     = valid ? (u32)((key[p] >> shift) & 0xFFull) : 256u;
+            const u32  d     = valid ? trr_digit(key[p], shift, qscale) : 256u;
             const u32  peers = __match_any_sync(MMG_FULL, d);  // (eight ballots instead: 25 % slower, profiles/r2h_*)
             if (valid) posB[hist[d * TRB_WARPS + w] + __popc(peers & ((1u << lane) - 1u))] = (unsigned short)p;
             __syncwarp();
@@ -431,7 +471,7 @@ __global__ void __launch_bounds__(TRB_THREADS)
                               PoseD pose, int use_pose, float r, u32 maxp, const u32* __restrict__ cnt, const u64* __restrict__ off, u64 off_base,
                               const u64* __restrict__ key, const float* __restrict__ hxyz, const u32* __restrict__ hidx, const u64* __restrict__ boff,
                               float* __restrict__ rxyz, float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt,
-                              u32* __restrict__ next_query, u32 n_small, u32 n_large)
+                              u32* __restrict__ next_query, u32 n_small, u32 n_large, float qscale)
 {
     constexpr unsigned short ACC = 1u << 15, SURV = 1u << 14, IDX = SURV - 1u;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -472,16 +512,33 @@ __global__ void __launch_bounds__(TRB_THREADS)
         }
         for (u32 i = threadIdx.x; i < N; i += blockDim.x) skey[i] = key[h0 + i];
         __syncthreads();
-        unsigned short* sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, 32);
-        if (threadIdx.x == 0) s_flag = 0;
-        __syncthreads();
-        {
-            bool tie = false;
-            for (u32 i = threadIdx.x; i + 1 < N; i += blockDim.x) tie |= (u32)(skey[sp[i]] >> 32) == (u32)(skey[sp[i + 1]] >> 32);
-            if (tie) s_flag = 1;
+        unsigned short* sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, qscale);
+        if (qscale > 0.f)
+        {   // exact (d2, rank) order inside the runs of equal q16: the thread that meets a run's head sorts the run
+            if (threadIdx.x == 0) s_flag = 0;
+            __syncthreads();
+            for (u32 i = threadIdx.x; i < N; i += blockDim.x)
+            {
+                const u32 qi = trr_q16(skey[sp[i]], qscale);
+                if ((i == 0 || trr_q16(skey[sp[i - 1]], qscale) != qi) && i + 1 < N && trr_q16(skey[sp[i + 1]], qscale) == qi)
+                {
+                    u32 e = i + 2;
+                    while (e < N && trr_q16(skey[sp[e]], qscale) == qi) e++;
+                    if (e - i > 64) s_flag = 1;
+                    else
+                        for (u32 a = i + 1; a < e; a++)
+                        {
+                            const unsigned short pa = sp[a];
+                            const u64            ka = skey[pa];
+                            u32                  b  = a;
+                            for (; b > i && skey[sp[b - 1]] > ka; b--) sp[b] = sp[b - 1];
+                            sp[b] = pa;
+                        }
+                }
+            }
+            __syncthreads();
+            if (s_flag) sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, 0.f);
         }
-        __syncthreads();
-        if (s_flag) sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, 0);
         auto K = [&](u32 i) -> u64 { return skey[sp[i] & IDX]; };
         if (maxp == 0)
         {   // (the flags of position i + 1 may be written while position i reads it: they sit above the index bits K() masks off)

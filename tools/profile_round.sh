@@ -16,6 +16,6 @@ if [ "$2" = "full" ]; then
 AB_STEPS=3 ncu --set full --clock-control none --import-source on -k regex:k_nn_ -s 9 -c 3 -o gpurun_out/${T}_prof_nn python tools/nn_ab.py nn_kernel=0 > gpurun_out/${T}_ncu2.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_insert_rank -s 2 -c 2 -o gpurun_out/${T}_prof_rank python bench.py --only insert_batched > gpurun_out/${T}_ncu3.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_insert_commit -s 2 -c 2 -o gpurun_out/${T}_prof_commit python bench.py --only insert_batched > gpurun_out/${T}_ncu4.log 2>&1
-compute-sanitizer --tool racecheck --print-limit 20 python tools/racecheck_insert.py > gpurun_out/${T}_racecheck_insert.log 2>&1; tail -5 gpurun_out/${T}_racecheck_insert.log
+# (compute-sanitizer is closed on this GPU pool: `compute-sanitizer --tool racecheck python tools/racecheck_insert.py` where it is open)
 fi
 cut -c1-300 gpurun_out/${T}_bench_n1.json
