@@ -248,6 +248,12 @@ int mmg::settle(const mmg_map* cm)
     if (!m->ctr_pending.load(std::memory_order_acquire)) return MMG_OK;
     std::lock_guard<std::mutex> lk(m->ctr_mtx);
     if (!m->ctr_pending.load(std::memory_order_relaxed)) return MMG_OK;
+    if (m->trees)
+    {   // SparseTrees keeps its own counters (mmg_trees.cu)
+        if (int rc = trees_settle(m)) return rc;
+        m->ctr_pending.store(false, std::memory_order_release);
+        return MMG_OK;
+    }
     MMG_CUDA(cudaEventSynchronize(m->ev_ctr));
     const Counters c  = *m->h_ctr;  // written by the last block of the last k_insert_commit
     m->h_nvox_hi      = c.nvox_hi;

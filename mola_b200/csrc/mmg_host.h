@@ -121,6 +121,7 @@ int sv_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, siz
 int trees_create(mmg_map* m);
 int trees_destroy(mmg_map* m);
 int trees_clear(mmg_map* m);
+int trees_settle(mmg_map* m);
 int trees_set_grid(mmg_map* m);
 int trees_clone(const mmg_map* src, mmg_map* dst);
 int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, size_t n, const double* pose12, int has_robot_pose, int mem,

@@ -387,15 +387,6 @@ __device__ __forceinline__ void nn_axis_gaps2(int c, float vsize, float q, float
     below = d0 * d0 * 0.9999f, above = d1 * d1 * 0.9999f;
 }
 
-// Two consecutive row slots with one 256-bit load (sm_100 LDG.256): half the load instructions and half the L1 tag
-// look-ups of the row walks, which ncu shows to be the busiest unit of these kernels (7 look-ups per warp load in
-// k_nn_tasks, 0.6 per SM cycle). Rows are 512-byte aligned and s is even, so the pair never straddles a 32-byte boundary.
-__device__ __forceinline__ void ld_row_pair(const float4* p, float4& a, float4& b)
-{
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
-        : "l"(p));
-}
 // nearest of the first `cnt` slots of a row: strict '<' in ascending slot order keeps the first minimum
 __device__ __forceinline__ void row_nearest(const float4* __restrict__ row, u32 cnt, const float3& p, float& cd, u32& cs)
 {

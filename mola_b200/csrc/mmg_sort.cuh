@@ -226,6 +226,76 @@ static __global__ void __launch_bounds__(RS_THREADS)
     }
 }
 
+// Small inputs (one lidar scan's kept points): all passes of the same stable LSD sort inside ONE launch of one
+// 1024-thread block, ping-ponging through the scratch arrays (L2-resident at these sizes). The multi-kernel pipeline
+// below costs three to five launches per 8-bit pass, each of them latency-bound at a few ten thousand keys.
+constexpr int RS_SMALL_THREADS = 1024, RS_SMALL_WARPS = RS_SMALL_THREADS / 32, RS_SMALL_MAX = 1 << 16;
+static __global__ void __launch_bounds__(RS_SMALL_THREADS)
+    k_radix_small(u32* k0, const u32* v0 /*nullable = iota*/, u32* k1, u32* va, u32* vb,  // no __restrict__: the arrays swap roles every pass
+                  u32 n, int passes, u32 clampv)
+{
+    __shared__ u32 cnt[RS_SMALL_WARPS][RS_RADIX];
+    __shared__ u32 sm[33];
+    const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u32      chunk = ((n + RS_SMALL_WARPS - 1) / RS_SMALL_WARPS + 31u) & ~31u;  // per warp, whole rounds of 32
+    const u32      beg = min(n, (u32)warp * chunk), end = min(n, beg + chunk);
+    u32 *          kin = k0, *kout = k1;
+    const u32*     vin  = v0;
+    u32*           vout = (v0 == va) ? vb : va;
+    for (int p = 0; p < passes; p++)
+    {
+        const int shift = p * RS_BITS;
+        for (int i = threadIdx.x; i < RS_SMALL_WARPS * RS_RADIX; i += RS_SMALL_THREADS) (&cnt[0][0])[i] = 0;
+        __syncthreads();
+        for (u32 j = beg + lane; j < end; j += 32) atomicAdd(&cnt[warp][(min(kin[j], clampv) >> shift) & (RS_RADIX - 1)], 1u);
+        __syncthreads();
+        {  // digit d of warp w starts at (keys with a smaller digit) + (keys with digit d in the warps before w)
+            u32 tot = 0;
+            if (threadIdx.x < RS_RADIX)
+                for (int w = 0; w < RS_SMALL_WARPS; w++) tot += cnt[w][threadIdx.x];
+            u32 all;
+            u32 run = block_exclusive_scan<u32>(threadIdx.x < RS_RADIX ? tot : 0u, sm, all);
+            if (threadIdx.x < RS_RADIX)
+                for (int w = 0; w < RS_SMALL_WARPS; w++)
+                {
+                    const u32 c         = cnt[w][threadIdx.x];
+                    cnt[w][threadIdx.x] = run;
+                    run += c;
+                }
+        }
+        __syncthreads();
+        for (u32 j0 = beg; j0 < end; j0 += 32)
+        {
+            const u32  j     = j0 + lane;
+            const bool valid = j < end;
+            const u32  key   = valid ? min(kin[j], clampv) : 0u;
+            const u32  digit = (key >> shift) & (RS_RADIX - 1);
+            const u32  peers = __match_any_sync(MMG_FULL, valid ? digit : (u32)RS_RADIX);
+            const int  leader = __ffs(peers) - 1;
+            u32        base  = 0;
+            if (valid && lane == leader)
+            {
+                base             = cnt[warp][digit];
+                cnt[warp][digit] = base + __popc(peers);
+            }
+            base = __shfl_sync(MMG_FULL, base, leader);
+            if (valid)
+            {
+                const u32 pos = base + __popc(peers & ((1u << lane) - 1));
+                kout[pos]     = key;
+                vout[pos]     = vin ? vin[j] : j;
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+        u32* t = kin;
+        kin    = kout;
+        kout   = t;
+        vin    = vout;
+        vout   = (vout == va) ? vb : va;
+    }
+}
+
 struct SortScratch
 {
     u32 *keys_b, *vals_a, *vals_b, *ghist, *bsum;  // keys_b/vals_*: n each; ghist: 256*nblocks; bsum: scan scratch
@@ -248,6 +318,21 @@ inline void radix_sort_pairs(u32* keys, const u32* vals_in, size_t n, u32 clampv
     u32 *      kin = keys, *kout = s.keys_b;
     const u32* vin  = vals_in;
     u32*       vout = (vals_in == s.vals_a) ? s.vals_b : s.vals_a;
+    if (n <= (size_t)RS_SMALL_MAX)
+    {
+        MMG_LAUNCH(k_radix_small, 1, RS_SMALL_THREADS, 0, st, kin, vin, kout, s.vals_a, s.vals_b, (u32)n, passes, clampv);
+        for (int p = 0; p < passes; p++)
+        {  // where the kernel's ping-pong ends
+            u32* t = kin;
+            kin    = kout;
+            kout   = t;
+            vin    = vout;
+            vout   = (vout == s.vals_a) ? s.vals_b : s.vals_a;
+        }
+        *sorted_keys = kin;
+        *sorted_vals = const_cast<u32*>(vin);
+        return;
+    }
     for (int p = 0; p < passes; p++)
     {
         const int shift = p * RS_BITS;

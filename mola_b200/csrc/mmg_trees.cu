@@ -20,6 +20,7 @@ struct TreesState
     u32            brow_hi = 0, bfree_n = 0, crow_hi = 0, cfree_n = 0, ncells = 0;
     u64            npoints = 0;
     TreesCounters* h_ctr   = nullptr;  // pinned mirror
+    cudaStream_t   pending_stream = nullptr;  // stream of the insert whose counters are still on their way (m->ctr_pending)
 };
 }  // namespace mmg
 
@@ -88,7 +89,7 @@ int ensure_chain_rows(mmg_map* m, u64 rows, cudaStream_t st)
 {
     TreesState* s = m->trees;
     if (rows <= s->crows) return MMG_OK;
-    const u64 nc = std::max<u64>(rows + rows / 2, 4096);
+    const u64 nc = std::max<u64>(2 * rows, 65536);  // 32 MB of rows at least, doubling: a map build sees a handful of copies
     int       rc;
     if ((rc = grow(&s->dev.cpts, s->crows * TR_ROW, nc * TR_ROW, 0, st))) return rc;
     if ((rc = grow(&s->dev.cnext, s->crows, nc, 0xFF, st))) return rc;
@@ -265,6 +266,7 @@ int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     const mmg_params& P = m->prm;
     int               rc;
     // eraseGridsFartherThan(:961-1000); the option is held in a float member (:893)
+    if (m->ctr_pending.load(std::memory_order_acquire) && ((rc = settle(m)))) return rc;
     const bool no_clearance = (has_robot_pose & MMG_INSERT_NO_CLEARANCE) != 0;
     has_robot_pose &= MMG_INSERT_ROBOT_POSE;
     if (has_robot_pose && pose12 && P.remove_voxels_farther_than > 0 && s->brow_hi > s->bfree_n)
@@ -299,60 +301,79 @@ int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     // u32 scratch: d2 | flag | pos (+ scan scratch) | bid | cslot | seg
     const size_t w1   = 6 * n + scan_scratch_elems(n) + 16;
     u32*         wrk  = (u32*)m->scratch_get(S_TREES1, w1 * sizeof(u32));
-    u32*         sbuf = (u32*)m->scratch_get(S_SORT, sort_scratch_words(n) * sizeof(u32));
+    u32*         sbuf = (u32*)m->scratch_get(S_SORT, 2 * sort_scratch_words(n) * sizeof(u32));
     if (!gp || !acc || !wrk || !sbuf) return MMG_ERR_OUT_OF_MEM;
     float* d2   = (float*)wrk;
     u32 *  flag = wrk + n, *pos = wrk + 2 * n, *bid = wrk + 3 * n + 1, *cslot = wrk + 4 * n + 1, *seg = wrk + 5 * n + 1, *bsum = wrk + 6 * n + 2;
     const SortScratch ss = sort_scratch_at(sbuf, n);
 
-    // phase 1: compose, nearest neighbour in the pre-batch map, clearance test
-    const PoseD T = make_pose(pose12);
-    MMG_LAUNCH(k_trees_compose, gN, 256, 0, st, dx, dy, dz, N, T, gp);
-    const float*   gq = (const float*)gp;
-    // the public insertPoint() appends without looking at the map (MMG_INSERT_NO_CLEARANCE): every d2 = 0 passes "d2 > -1"
-    if (no_clearance) MMG_CUDA(cudaMemsetAsync(d2, 0, n * sizeof(float), st));
-    else if ((rc = launch_trees_nn1(m, gq, gq + 1, gq + 2, n, 4u, T, 0, -1.0f, (uint8_t*)nullptr, (float*)nullptr, d2, (u64*)nullptr, st))) return rc;
+    // phase 1: compose + clearance test against the pre-batch map, compaction of the kept points, block find-or-insert.
+    // One host round trip per scan: the counters read here size everything phase 2 needs.
+    const PoseD T   = make_pose(pose12);
     const float thr = no_clearance ? -1.0f : P.minimum_points_clearance * P.minimum_points_clearance;
+    // the public insertPoint() appends without looking at the map (MMG_INSERT_NO_CLEARANCE): every d2 = 0 passes "d2 > -1"
+    if (no_clearance)
+    {
+        MMG_LAUNCH(k_trees_compose, gN, 256, 0, st, dx, dy, dz, N, T, gp);
+        MMG_CUDA(cudaMemsetAsync(d2, 0, n * sizeof(float), st));
+    }
+    else
+    {
+        u32* todo = (u32*)m->scratch_get(S_TREES_TODO, (n + 1) * sizeof(u32));
+        if (!todo) return MMG_ERR_OUT_OF_MEM;
+        MMG_CUDA(cudaMemsetAsync(todo + n, 0, sizeof(u32), st));
+        MMG_LAUNCH(k_trees_clear, gN, 256, 0, st, s->dev, dx, dy, dz, N, T, thr, gp, d2, todo, todo + n);
+        // the points the 3x3x3 cell region could not decide (none at centimetre clearances): exact search
+        const float* gq = (const float*)gp;
+        MMG_LAUNCH(k_trees_nn1, persistent_blocks(m, n, 8, 8), 256, 0, st, s->dev, gq, gq + 1, gq + 2, N, 4u, T, 0, -1.0f, (uint8_t*)nullptr, (float*)nullptr,
+                   d2, (u64*)nullptr, (const u32*)todo, (const u32*)(todo + n));
+    }
     MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->oob, 0, sizeof(u32), st));
     MMG_LAUNCH(k_trees_flags, gN, 256, 0, st, s->dev, gp, d2, N, thr, flag);
-    exclusive_scan<u32, u32>(flag, pos, n, pos + n, bsum, st);
-    u32 nacc = 0;
-    MMG_CUDA(cudaMemcpyAsync(&nacc, pos + n, sizeof(u32), cudaMemcpyDeviceToHost, st));
-    if ((rc = read_ctr(m, st))) return rc;  // synchronises; also fetches the out-of-range count
+    exclusive_scan<u32, u32>(flag, pos, n, &s->dev.ctr->nacc, bsum, st);
+    if ((rc = ensure_btab(m, (u64)(s->brow_hi - s->bfree_n) + n, st))) return rc;  // every kept point could open a block
+    MMG_LAUNCH(k_trees_locate, gN, 256, 0, st, s->dev, gp, flag, pos, N, acc, bid);
+    if ((rc = read_ctr(m, st))) return rc;  // synchronises: kept points, block rows in use, out-of-range count
+    const u32 nacc = s->h_ctr->nacc, oob = s->h_ctr->oob;
     if (nacc)
     {
-        // phase 2a: blocks
-        if ((rc = ensure_btab(m, (u64)(s->brow_hi - s->bfree_n) + nacc, st))) return rc;
-        MMG_LAUNCH(k_trees_locate, gN, 256, 0, st, s->dev, gp, flag, pos, N, acc, bid);
-        if ((rc = read_ctr(m, st))) return rc;
+        // phase 2 (no further round trip): block-local indices, cells, chain rows. The rows a batch can take are bounded
+        // by one per touched cell plus one per 32 points, so the capacity is reserved before the kernels run.
         if ((rc = ensure_block_rows(m, s->brow_hi, st))) return rc;
-        u32* segse = (u32*)m->scratch_get(S_TREES2, 2 * (size_t)s->brows * sizeof(u32));
-        if (!segse) return MMG_ERR_OUT_OF_MEM;
-        u32 *         sbid, *sidx;
+        if ((rc = ensure_ctab(m, (u64)s->ncells + nacc, st))) return rc;
+        if ((rc = ensure_chain_rows(m, (u64)s->crow_hi + nacc + nacc / TR_ROW + 2, st))) return rc;
+        u32 *          sbid, *sidx, *sslot, *sidx2;
         const unsigned gA = (nacc + 255) / 256;
         radix_sort_index(bid, nacc, s->brow_hi, ss, &sbid, &sidx, st);
-        MMG_LAUNCH(k_trees_block_segs, gA, 256, 0, st, sbid, nacc, segse, segse + s->brows);
-        // phase 2b: block-local indices, cells
-        if ((rc = ensure_ctab(m, (u64)s->ncells + nacc, st))) return rc;
-        MMG_LAUNCH(k_trees_assign, gA, 256, 0, st, s->dev, sbid, sidx, nacc, segse, acc, cslot);
-        MMG_LAUNCH(k_trees_commit_blocks, gA, 256, 0, st, s->dev, sbid, sidx, nacc, segse, segse + s->brows, acc);
-        u32 *sslot, *sidx2;
-        radix_sort_index(cslot, nacc, (u32)(s->ccap - 1), ss, &sslot, &sidx2, st);
-        MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->nseg, 0, 2 * sizeof(u32), st));  // nseg, need_rows
-        MMG_LAUNCH(k_trees_cell_heads, gA, 256, 0, st, s->dev, sslot, nacc, seg);
-        MMG_LAUNCH(k_trees_cell_need, gA, 256, 0, st, s->dev, sslot, nacc, seg);
-        if ((rc = read_ctr(m, st))) return rc;
-        if ((rc = ensure_chain_rows(m, (u64)s->crow_hi + s->h_ctr->need_rows, st))) return rc;
-        const unsigned ab = persistent_blocks(m, s->h_ctr->nseg, 8, 8);
-        MMG_LAUNCH(k_trees_append, ab, 256, 0, st, s->dev, sslot, sidx2, nacc, seg, acc);
-        if ((rc = read_ctr(m, st))) return rc;
+        MMG_LAUNCH(k_trees_assign, gA, 256, 0, st, s->dev, sbid, sidx, nacc, acc, cslot);
+        // the second sort must not overwrite the first one's result (k_trees_heads_commit reads both)
+        const SortScratch ss2 = sort_scratch_at(sbuf + sort_scratch_words(n), n);
+        radix_sort_index(cslot, nacc, (u32)(s->ccap - 1), ss2, &sslot, &sidx2, st);
+        MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->nseg, 0, sizeof(u32), st));
+        MMG_LAUNCH(k_trees_heads_commit, gA, 256, 0, st, s->dev, sbid, sidx, sslot, nacc, acc, seg);
+        MMG_LAUNCH(k_trees_append, persistent_blocks(m, nacc, 8, 8), 256, 0, st, s->dev, sslot, sidx2, nacc, seg, acc);
+        // the counters the append moves (chain rows, cells, points) reach the host mirrors lazily: settle()
+        MMG_CUDA(cudaMemcpyAsync(s->h_ctr, s->dev.ctr, sizeof(TreesCounters), cudaMemcpyDeviceToHost, st));
+        MMG_CUDA(cudaEventRecord(m->ev_ctr, st));
+        s->pending_stream = st;
+        m->ctr_pending.store(true, std::memory_order_release);
     }
     MMG_CUDA(cudaGetLastError());
-    if (s->h_ctr->oob)
+    if (oob)
     {
-        set_error("%u of %zu points have a block index outside +-2^20 and were skipped", s->h_ctr->oob, n);
+        set_error("%u of %zu points have a block index outside +-2^20 and were skipped", oob, n);
         return MMG_ERR_OUT_OF_RANGE;
     }
+    return MMG_OK;
+}
+
+// The host mirrors after an insert that returned without waiting for its last kernels (called by mmg::settle()).
+int trees_settle(mmg_map* m)
+{
+    TreesState* s = m->trees;
+    MMG_CUDA(cudaEventSynchronize(m->ev_ctr));
+    s->brow_hi = s->h_ctr->brow_hi, s->bfree_n = s->h_ctr->bfree_n, s->crow_hi = s->h_ctr->crow_hi, s->cfree_n = s->h_ctr->cfree_n;
+    s->ncells = s->h_ctr->ncells, s->npoints = s->h_ctr->npoints;
     return MMG_OK;
 }
 

@@ -38,9 +38,9 @@ struct TreesCounters
     u32 ncells;            // live cell entries
     u32 oob;
     u32 nseg;
-    u32 need_rows;         // rows the current batch will allocate
+    u32 need_rows;         // (unused since the append reserves rows by an upper bound)
     u32 maxcnt;            // scratch for reductions
-    u32 pad;
+    u32 nacc;              // points the current batch keeps (total of the flag scan)
     unsigned long long npoints;
 };
 
@@ -491,6 +491,75 @@ static __global__ void k_trees_compose(const float* __restrict__ xs, const float
     const float3 g = compose_point(pose, xs[i], ys[i], zs[i]);
     gp[i]          = make_float4(g.x, g.y, g.z, 0.f);
 }
+// Clearance test of phase 1 in one pass, one THREAD per input point: compose, then ask whether the pre-batch map holds
+// ANY point of the same block with d2 <= thr (= the reference's "nearest neighbour has d2 <= clearance^2": the nearest
+// one is within thr iff some point is). Only the fine cells whose box can reach thr are opened, and the walk stops at
+// the first such point. Writes the composed point and d2 = that point's distance (<= thr: rejected by k_trees_flags)
+// or -1 ("none": kept). When thr reaches past the 3x3x3 cell region (clearance of the order of the 0.31 m cells) the
+// region cannot certify "none": those points go to `todo` for the exact search (k_trees_nn1).
+static __global__ void __launch_bounds__(256)
+    k_trees_clear(TreesDev t, const float* __restrict__ xs, const float* __restrict__ ys, const float* __restrict__ zs, u32 n, PoseD pose, float thr,
+                  float4* __restrict__ gp, float* __restrict__ d2, u32* __restrict__ todo, u32* __restrict__ ntodo)
+{
+    const u32 q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const float3 p = compose_point(pose, xs[q], ys[q], zs[q]);
+    gp[q]          = make_float4(p.x, p.y, p.z, 0.f);
+    int   kx, ky, kz;
+    u32   bid = 0;
+    float hit = -1.0f;
+    bool  sure = true;
+    if (trees_find_block(t, p.x, p.y, p.z, kx, ky, kz, bid))
+    {
+        const BlockGeom g     = trees_geom(t, kx, ky, kz);
+        const float     qv[3] = {p.x, p.y, p.z};
+        int             c0[3];
+#pragma unroll
+        for (int a = 0; a < 3; a++) c0[a] = trees_cell_axis(g, a, qv[a]);
+        for (int it = 0; it < 27 && hit < 0.f; it++)
+        {
+            const int j = it == 0 ? 13 : (it <= 13 ? it - 1 : it);
+            const int x = c0[0] + j / 9 - 1, y = c0[1] + (j / 3) % 3 - 1, z = c0[2] + j % 3 - 1;
+            if (x < 0 || x > 31 || y < 0 || y > 31 || z < 0 || z > 31) continue;
+            if (it && trees_box_lb(g, qv, x, y, z, 1) > thr) continue;
+            const u32 cell = trees_cell_id(x, y, z);
+            if (!((__ldg(&t.l0[(size_t)bid * 1024 + (cell >> 5)]) >> (cell & 31)) & 1u)) continue;
+            u32 head, cnt;
+            if (!probe_ro(t.ctab, t.cmask, trees_cell_key(bid, cell), head, cnt) || cnt == 0) continue;
+            u32 fill = ((cnt - 1) & (TR_ROW - 1)) + 1, row = head;
+            for (u32 r = 0, nrows = (cnt + TR_ROW - 1) / TR_ROW; r < nrows && hit < 0.f; r++)
+            {
+                const float4* rp = t.cpts + (size_t)row * TR_ROW;
+                for (u32 s = 0; s < fill; s += 2)
+                {   // two slots per 256-bit load (a row is 512 B aligned; the slot past `fill` is never looked at)
+                    float4 a, b;
+                    ld_row_pair(rp + s, a, b);
+                    const float da = sqr_dist(qv[0], qv[1], qv[2], a.x, a.y, a.z);
+                    const float db = sqr_dist(qv[0], qv[1], qv[2], b.x, b.y, b.z);
+                    if (da <= thr) { hit = da; break; }
+                    if (s + 1 < fill && db <= thr) { hit = db; break; }
+                }
+                row  = __ldg(&t.cnext[row]);
+                fill = TR_ROW;
+            }
+        }
+        if (hit < 0.f)
+        {
+            float out = __int_as_float(0x7f800000);
+#pragma unroll
+            for (int a = 0; a < 3; a++)
+            {
+                const int   lo_c = max(c0[a] - 1, 0), hi_c = min(c0[a] + 1, 31);
+                const float mg   = 8.f * g.margin[a];
+                if (lo_c > 0) out = fminf(out, fmaxf(0.f, qv[a] - (g.lo[a] + (float)lo_c * g.cs[a]) - mg));
+                if (hi_c < 31) out = fminf(out, fmaxf(0.f, (g.lo[a] + (float)(hi_c + 1) * g.cs[a]) - qv[a] - mg));
+            }
+            sure = thr < out * out * 0.9999f;
+        }
+    }
+    if (sure) d2[q] = hit;
+    else todo[atomicAdd(ntodo, 1u)] = q;
+}
 static __global__ void k_trees_flags(TreesDev t, const float4* __restrict__ gp, const float* __restrict__ d2, u32 n, float thr, u32* __restrict__ flag)
 {
     const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -585,19 +654,22 @@ static __global__ void __launch_bounds__(256)
     }
     warp_bbox6(t.bbox, keep, p.x, p.y, p.z);
 }
-// sorted-by-block list -> first / one-past-last position of every block's segment
-static __global__ void k_trees_block_segs(const u32* __restrict__ sbid, u32 n, u32* __restrict__ segstart, u32* __restrict__ segend)
+// first position of value b in the ascending list sbid[0, n)
+__device__ __forceinline__ u32 trees_lower_bound(const u32* __restrict__ sbid, u32 n, u32 b)
 {
-    const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= n) return;
-    const u32 b = sbid[e];
-    if (e == 0 || sbid[e - 1] != b) segstart[b] = e;
-    if (e + 1 == n || sbid[e + 1] != b) segend[b] = e + 1;
+    u32 lo = 0, hi = n;
+    while (lo < hi)
+    {
+        const u32 mid = (lo + hi) >> 1;
+        if (__ldg(sbid + mid) < b) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
 }
-// block-local index + fine cell + cell find-or-insert for every kept point (sorted order e)
+// block-local index + fine cell + cell find-or-insert for every kept point (e = position in the list sorted by block;
+// the sort is stable, so e - (first position of the block) is the point's rank among the block's kept points)
 static __global__ void __launch_bounds__(256)
-    k_trees_assign(TreesDev t, const u32* __restrict__ sbid, const u32* __restrict__ sidx, u32 n, const u32* __restrict__ segstart, float4* __restrict__ acc,
-                   u32* __restrict__ cslot)
+    k_trees_assign(TreesDev t, const u32* __restrict__ sbid, const u32* __restrict__ sidx, u32 n, float4* __restrict__ acc, u32* __restrict__ cslot)
 {
     const u32  e     = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = e < n;
@@ -608,7 +680,7 @@ static __global__ void __launch_bounds__(256)
         const u32 bid = sbid[e];
         j             = sidx[e];
         float4 p      = acc[j];
-        p.w           = __uint_as_float(t.bcnt[bid] + (e - segstart[bid]));
+        p.w           = __uint_as_float(t.bcnt[bid] + (e - trees_lower_bound(sbid, n, bid)));
         acc[j]        = p;
         int kx, ky, kz;
         trees_index(t, p.x, kx), trees_index(t, p.y, ky), trees_index(t, p.z, kz);
@@ -623,40 +695,32 @@ static __global__ void __launch_bounds__(256)
     slot = __shfl_sync(MMG_FULL, slot, leader);
     if (valid) cslot[j] = (u32)slot;
 }
-// after k_trees_assign: publish the new block counts and keys
-static __global__ void k_trees_commit_blocks(TreesDev t, const u32* __restrict__ sbid, const u32* __restrict__ sidx, u32 n, const u32* __restrict__ segstart,
-                                             const u32* __restrict__ segend, const float4* __restrict__ acc)
+// After k_trees_assign, one thread per kept point, two independent jobs:
+//  - position e of the list sorted by block: the first point of a block publishes the block's key and new count;
+//  - position e of the list sorted by cell slot: the first point of a cell's segment enters it in the segment list.
+static __global__ void __launch_bounds__(256)
+    k_trees_heads_commit(TreesDev t, const u32* __restrict__ sbid, const u32* __restrict__ sidx, const u32* __restrict__ sslot, u32 n,
+                         const float4* __restrict__ acc, u32* __restrict__ seg_start)
 {
     const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
+    const u32 s = sslot[e];
+    if (e == 0 || sslot[e - 1] != s) seg_start[atomicAdd(&t.ctr->nseg, 1u)] = e;
     const u32 b = sbid[e];
     if (e != 0 && sbid[e - 1] == b) return;
+    u32 lo = e + 1, hi = n;  // one past the block's last point
+    while (lo < hi)
+    {
+        const u32 mid = (lo + hi) >> 1;
+        if (__ldg(sbid + mid) <= b) lo = mid + 1;
+        else hi = mid;
+    }
     const float4 p = acc[sidx[e]];
     int          kx, ky, kz;
     trees_index(t, p.x, kx), trees_index(t, p.y, ky), trees_index(t, p.z, kz);
     t.bkey[b] = pack_key(kx, ky, kz);
-    t.bcnt[b] += segend[b] - segstart[b];
-    atomicAdd(&t.ctr->npoints, (unsigned long long)(segend[b] - segstart[b]));
-}
-
-// Segment heads of the list sorted by cell slot (any order) + chain rows the batch will need.
-static __global__ void k_trees_cell_heads(TreesDev t, const u32* __restrict__ sslot, u32 n, u32* __restrict__ seg_start)
-{
-    const u32 j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
-    const u32 s = sslot[j];
-    if (j != 0 && sslot[j - 1] == s) return;
-    seg_start[atomicAdd(&t.ctr->nseg, 1u)] = j;
-}
-static __global__ void k_trees_cell_need(TreesDev t, const u32* __restrict__ sslot, u32 n, const u32* __restrict__ seg_start)
-{
-    const u32 s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= t.ctr->nseg) return;
-    const u32 j0 = seg_start[s], slot = sslot[j0];
-    u32       len = 1;
-    while (j0 + len < n && sslot[j0 + len] == slot) len++;
-    const u32 cnt = t.ctab[slot].cnt;
-    atomicAdd(&t.ctr->need_rows, (cnt + len + TR_ROW - 1) / TR_ROW - (cnt + TR_ROW - 1) / TR_ROW);
+    t.bcnt[b] += lo - e;
+    atomicAdd(&t.ctr->npoints, (unsigned long long)(lo - e));
 }
 // One warp per touched cell: appends the cell's batch points to its chain. The head row is the
 // newest and the only partially filled one; new rows are linked in front of it.
