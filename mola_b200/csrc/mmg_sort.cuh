@@ -247,7 +247,15 @@ static __global__ void __launch_bounds__(RS_SMALL_THREADS)
         const int shift = p * RS_BITS;
         for (int i = threadIdx.x; i < RS_SMALL_WARPS * RS_RADIX; i += RS_SMALL_THREADS) (&cnt[0][0])[i] = 0;
         __syncthreads();
-        for (u32 j = beg + lane; j < end; j += 32) atomicAdd(&cnt[warp][(min(kin[j], clampv) >> shift) & (RS_RADIX - 1)], 1u);
+        for (u32 j0 = beg + lane; j0 < end; j0 += 32 * 8)
+        {   // eight independent loads in flight per lane
+            u32 k[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) k[i] = (j0 + 32 * i < end) ? kin[j0 + 32 * i] : 0u;
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                if (j0 + 32 * i < end) atomicAdd(&cnt[warp][(min(k[i], clampv) >> shift) & (RS_RADIX - 1)], 1u);
+        }
         __syncthreads();
         {  // digit d of warp w starts at (keys with a smaller digit) + (keys with digit d in the warps before w)
             u32 tot = 0;
@@ -264,28 +272,41 @@ static __global__ void __launch_bounds__(RS_SMALL_THREADS)
                 }
         }
         __syncthreads();
-        for (u32 j0 = beg; j0 < end; j0 += 32)
-        {
-            const u32  j     = j0 + lane;
-            const bool valid = j < end;
-            const u32  key   = valid ? min(kin[j], clampv) : 0u;
-            const u32  digit = (key >> shift) & (RS_RADIX - 1);
-            const u32  peers = __match_any_sync(MMG_FULL, valid ? digit : (u32)RS_RADIX);
-            const int  leader = __ffs(peers) - 1;
-            u32        base  = 0;
-            if (valid && lane == leader)
+        for (u32 jb = beg; jb < end; jb += 32 * 4)
+        {   // four rounds of 32 keys loaded ahead, then ranked round by round (input order)
+            u32 kk[4], vv[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++)
             {
-                base             = cnt[warp][digit];
-                cnt[warp][digit] = base + __popc(peers);
+                const u32 j = jb + 32 * i + lane;
+                kk[i]       = (j < end) ? kin[j] : 0u;
+                vv[i]       = (j < end && vin) ? vin[j] : j;
             }
-            base = __shfl_sync(MMG_FULL, base, leader);
-            if (valid)
+#pragma unroll
+            for (int i = 0; i < 4; i++)
             {
-                const u32 pos = base + __popc(peers & ((1u << lane) - 1));
-                kout[pos]     = key;
-                vout[pos]     = vin ? vin[j] : j;
+                const u32 j = jb + 32 * i + lane;
+                if (jb + 32 * i >= end) break;  // warp-uniform
+                const bool valid = j < end;
+                const u32  key   = valid ? min(kk[i], clampv) : 0u;
+                const u32  digit = (key >> shift) & (RS_RADIX - 1);
+                const u32  peers = __match_any_sync(MMG_FULL, valid ? digit : (u32)RS_RADIX);
+                const int  leader = __ffs(peers) - 1;
+                u32        base  = 0;
+                if (valid && lane == leader)
+                {
+                    base             = cnt[warp][digit];
+                    cnt[warp][digit] = base + __popc(peers);
+                }
+                base = __shfl_sync(MMG_FULL, base, leader);
+                if (valid)
+                {
+                    const u32 pos = base + __popc(peers & ((1u << lane) - 1));
+                    kout[pos]     = key;
+                    vout[pos]     = vv[i];
+                }
+                __syncwarp();
             }
-            __syncwarp();
         }
         __syncthreads();
         u32* t = kin;

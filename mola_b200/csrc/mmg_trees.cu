@@ -20,6 +20,8 @@ struct TreesState
     u32            brow_hi = 0, bfree_n = 0, crow_hi = 0, cfree_n = 0, ncells = 0;
     u64            npoints = 0;
     TreesCounters* h_ctr   = nullptr;  // pinned mirror
+    uint4*         cwork = nullptr;  // one work word set per cell-table slot (k_trees_assign / k_trees_rows), sized like ctab
+    u64            cwork_cap = 0;
     cudaStream_t   pending_stream = nullptr;  // stream of the insert whose counters are still on their way (m->ctr_pending)
 };
 }  // namespace mmg
@@ -164,6 +166,7 @@ int trees_destroy(mmg_map* m)
     if (!s) return MMG_OK;
     cudaFree(s->dev.btab), cudaFree(s->dev.bkey), cudaFree(s->dev.bcnt), cudaFree(s->dev.l1), cudaFree(s->dev.l0), cudaFree(s->dev.bfree);
     cudaFree(s->dev.ctab), cudaFree(s->dev.cpts), cudaFree(s->dev.cnext), cudaFree(s->dev.cfree), cudaFree(s->dev.ctr);
+    if (s->cwork) cudaFree(s->cwork);
     if (s->h_ctr) cudaFreeHost(s->h_ctr);
     delete s;
     m->trees = nullptr;
@@ -301,7 +304,7 @@ int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     // u32 scratch: d2 | flag | pos (+ scan scratch) | bid | cslot | seg
     const size_t w1   = 6 * n + scan_scratch_elems(n) + 16;
     u32*         wrk  = (u32*)m->scratch_get(S_TREES1, w1 * sizeof(u32));
-    u32*         sbuf = (u32*)m->scratch_get(S_SORT, 2 * sort_scratch_words(n) * sizeof(u32));
+    u32*         sbuf = (u32*)m->scratch_get(S_SORT, sort_scratch_words(n) * sizeof(u32));
     if (!gp || !acc || !wrk || !sbuf) return MMG_ERR_OUT_OF_MEM;
     float* d2   = (float*)wrk;
     u32 *  flag = wrk + n, *pos = wrk + 2 * n, *bid = wrk + 3 * n + 1, *cslot = wrk + 4 * n + 1, *seg = wrk + 5 * n + 1, *bsum = wrk + 6 * n + 2;
@@ -342,16 +345,29 @@ int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, 
         if ((rc = ensure_block_rows(m, s->brow_hi, st))) return rc;
         if ((rc = ensure_ctab(m, (u64)s->ncells + nacc, st))) return rc;
         if ((rc = ensure_chain_rows(m, (u64)s->crow_hi + nacc + nacc / TR_ROW + 2, st))) return rc;
-        u32 *          sbid, *sidx, *sslot, *sidx2;
+        if (s->cwork_cap != s->ccap)
+        {   // per-slot work words of the cell table (batch ordinals, then the owner's row bookkeeping); all zero between batches
+            MMG_CUDA(cudaStreamSynchronize(st));
+            if (s->cwork) cudaFree(s->cwork);
+            s->cwork = nullptr, s->cwork_cap = 0;
+            if (cudaMalloc(&s->cwork, s->ccap * sizeof(uint4)) != cudaSuccess)
+            {
+                set_error("cudaMalloc(%llu B) failed", (unsigned long long)(s->ccap * sizeof(uint4)));
+                cudaGetLastError();
+                return MMG_ERR_OUT_OF_MEM;
+            }
+            MMG_CUDA(cudaMemsetAsync(s->cwork, 0, s->ccap * sizeof(uint4), st));
+            s->cwork_cap = s->ccap;
+        }
+        u32 *          sbid, *sidx;
         const unsigned gA = (nacc + 255) / 256;
         radix_sort_index(bid, nacc, s->brow_hi, ss, &sbid, &sidx, st);
-        MMG_LAUNCH(k_trees_assign, gA, 256, 0, st, s->dev, sbid, sidx, nacc, acc, cslot);
-        // the second sort must not overwrite the first one's result (k_trees_heads_commit reads both)
-        const SortScratch ss2 = sort_scratch_at(sbuf + sort_scratch_words(n), n);
-        radix_sort_index(cslot, nacc, (u32)(s->ccap - 1), ss2, &sslot, &sidx2, st);
-        MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->nseg, 0, sizeof(u32), st));
-        MMG_LAUNCH(k_trees_heads_commit, gA, 256, 0, st, s->dev, sbid, sidx, sslot, nacc, acc, seg);
-        MMG_LAUNCH(k_trees_append, persistent_blocks(m, nacc, 8, 8), 256, 0, st, s->dev, sslot, sidx2, nacc, seg, acc);
+        u32* ord = seg;
+        MMG_CUDA(launch_pdl(k_trees_assign, gA, 256, st, s->dev, (const u32*)sbid, (const u32*)sidx, nacc, acc, s->cwork, cslot, ord));
+        MMG_CUDA(launch_pdl(k_trees_rows, gA, 256, st, s->dev, (const u32*)sbid, (const u32*)sidx, (const u32*)cslot, (const u32*)ord, nacc,
+                            (const float4*)acc, s->cwork));
+        MMG_CUDA(launch_pdl(k_trees_write, gA, 256, st, s->dev, (const u32*)sidx, (const u32*)cslot, (const u32*)ord, nacc, (const float4*)acc,
+                            (const uint4*)s->cwork));
         // the counters the append moves (chain rows, cells, points) reach the host mirrors lazily: settle()
         MMG_CUDA(cudaMemcpyAsync(s->h_ctr, s->dev.ctr, sizeof(TreesCounters), cudaMemcpyDeviceToHost, st));
         MMG_CUDA(cudaEventRecord(m->ev_ctr, st));

@@ -529,17 +529,21 @@ static __global__ void __launch_bounds__(256)
             u32 fill = ((cnt - 1) & (TR_ROW - 1)) + 1, row = head;
             for (u32 r = 0, nrows = (cnt + TR_ROW - 1) / TR_ROW; r < nrows && hit < 0.f; r++)
             {
-                const float4* rp = t.cpts + (size_t)row * TR_ROW;
-                for (u32 s = 0; s < fill; s += 2)
-                {   // two slots per 256-bit load (a row is 512 B aligned; the slot past `fill` is never looked at)
-                    float4 a, b;
-                    ld_row_pair(rp + s, a, b);
-                    const float da = sqr_dist(qv[0], qv[1], qv[2], a.x, a.y, a.z);
-                    const float db = sqr_dist(qv[0], qv[1], qv[2], b.x, b.y, b.z);
-                    if (da <= thr) { hit = da; break; }
-                    if (s + 1 < fill && db <= thr) { hit = db; break; }
+                const float4* rp  = t.cpts + (size_t)row * TR_ROW;
+                const u32     nxt = (r + 1 < nrows) ? __ldg(&t.cnext[row]) : 0u;  // in flight together with the row
+                for (u32 s = 0; s < fill && hit < 0.f; s += 8)
+                {   // eight slots per step, four independent 256-bit loads (slots past `fill` are loaded but never looked at)
+                    float4 c[8];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) ld_row_pair(rp + s + 2 * k, c[2 * k], c[2 * k + 1]);
+#pragma unroll
+                    for (int k = 0; k < 8; k++)
+                    {
+                        const float d = sqr_dist(qv[0], qv[1], qv[2], c[k].x, c[k].y, c[k].z);
+                        if (s + k < fill && d <= thr && hit < 0.f) hit = d;
+                    }
                 }
-                row  = __ldg(&t.cnext[row]);
+                row  = nxt;
                 fill = TR_ROW;
             }
         }
@@ -666,20 +670,30 @@ __device__ __forceinline__ u32 trees_lower_bound(const u32* __restrict__ sbid, u
     }
     return lo;
 }
-// block-local index + fine cell + cell find-or-insert for every kept point (e = position in the list sorted by block;
-// the sort is stable, so e - (first position of the block) is the point's rank among the block's kept points)
+// Phase 2 of the insert, three kernels over the kept points in block order (e = position in the list sorted by block;
+// the sort is stable, so e - (first position of the block) is the point's rank among the block's kept points):
+//   k_trees_assign  block-local index, fine cell, cell find-or-insert, and the point's ordinal among the batch points
+//                   of its cell (a counter per cell slot in `cwork[slot].w`, zero between batches);
+//   k_trees_rows    ordinal 0 = the cell's owner: links the chain rows the cell's batch points need in front of the head
+//                   (several rows come as one contiguous run), publishes the new head and count, and leaves
+//                   {old count, old head, first new row} in cwork[slot]; the first point of a block publishes the block;
+//   k_trees_write   every point stores itself at slot (old count + ordinal) of its cell.
+// The order of a cell's points inside its rows is the order of the ordinals (arbitrary): queries order by
+// (d2, block-local index) and the export by block-local index, never by the position in a row.
 static __global__ void __launch_bounds__(256)
-    k_trees_assign(TreesDev t, const u32* __restrict__ sbid, const u32* __restrict__ sidx, u32 n, float4* __restrict__ acc, u32* __restrict__ cslot)
+    k_trees_assign(TreesDev t, const u32* __restrict__ sbid, const u32* __restrict__ sidx, u32 n, float4* __restrict__ acc, uint4* __restrict__ cwork,
+                   u32* __restrict__ cslot, u32* __restrict__ ord)
 {
+    pdl_trigger();
+    pdl_wait();
     const u32  e     = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = e < n;
     u64        key   = KEY_EMPTY;
-    u32        j     = 0;
     if (valid)
     {
         const u32 bid = sbid[e];
-        j             = sidx[e];
-        float4 p      = acc[j];
+        const u32 j   = sidx[e];
+        float4    p   = acc[j];
         p.w           = __uint_as_float(t.bcnt[bid] + (e - trees_lower_bound(sbid, n, bid)));
         acc[j]        = p;
         int kx, ky, kz;
@@ -690,22 +704,53 @@ static __global__ void __launch_bounds__(256)
     const u32 peers  = __match_any_sync(MMG_FULL, key);
     const int leader = __ffs(peers) - 1;
     u64       slot   = 0;
+    u32       base   = 0;
     if (valid && lane_id() == leader)
+    {
         trees_find_or_insert(t.ctab, t.cmask, key, [&]() { atomicAdd(&t.ctr->ncells, 1u); return 0xFFFFFFFEu; /* "no chain yet" */ }, &slot);
+        base = atomicAdd(&cwork[slot].w, (u32)__popc(peers));
+    }
     slot = __shfl_sync(MMG_FULL, slot, leader);
-    if (valid) cslot[j] = (u32)slot;
+    base = __shfl_sync(MMG_FULL, base, leader);
+    if (valid)
+    {
+        cslot[e] = (u32)slot;
+        ord[e]   = base + __popc(peers & ((1u << lane_id()) - 1));
+    }
 }
-// After k_trees_assign, one thread per kept point, two independent jobs:
-//  - position e of the list sorted by block: the first point of a block publishes the block's key and new count;
-//  - position e of the list sorted by cell slot: the first point of a cell's segment enters it in the segment list.
 static __global__ void __launch_bounds__(256)
-    k_trees_heads_commit(TreesDev t, const u32* __restrict__ sbid, const u32* __restrict__ sidx, const u32* __restrict__ sslot, u32 n,
-                         const float4* __restrict__ acc, u32* __restrict__ seg_start)
+    k_trees_rows(TreesDev t, const u32* __restrict__ sbid, const u32* __restrict__ sidx, const u32* __restrict__ cslot, const u32* __restrict__ ord, u32 n,
+                 const float4* __restrict__ acc, uint4* __restrict__ cwork)
 {
+    pdl_trigger();
+    pdl_wait();
     const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
-    const u32 s = sslot[e];
-    if (e == 0 || sslot[e - 1] != s) seg_start[atomicAdd(&t.ctr->nseg, 1u)] = e;
+    if (ord[e] == 0)
+    {
+        const u32 slot = cslot[e];
+        Entry*    en   = t.ctab + slot;
+        const u32 cnt = en->cnt, len = cwork[slot].w;
+        u32       head = en->vid;
+        if (cnt == 0)
+        {  // first points of this cell: publish it in the occupancy masks
+            head           = VID_INVALID;
+            const u32 bid  = (u32)(en->key >> 15), cell = (u32)(en->key & (TR_CELLS - 1));
+            atomicOr(&t.l0[(size_t)bid * 1024 + (cell >> 5)], 1u << (cell & 31));
+            atomicOr(&t.l1[(size_t)bid * 16 + (cell >> 11)], 1u << ((cell >> 6) & 31));
+        }
+        const u32 have = (cnt + TR_ROW - 1) / TR_ROW, need = (cnt + len + TR_ROW - 1) / TR_ROW - have;
+        u32       first = 0;
+        if (need)
+        {
+            first = need == 1 ? trees_alloc(&t.ctr->cfree_n, &t.ctr->crow_hi, t.cfree) : atomicAdd(&t.ctr->crow_hi, need);
+            t.cnext[first] = head;
+            for (u32 r = 1; r < need; r++) t.cnext[first + r] = first + r - 1;
+            en->vid = first + need - 1;  // the newest row is the head and the only partially filled one
+        }
+        en->cnt     = cnt + len;
+        cwork[slot] = make_uint4(cnt, head, first, 0u);
+    }
     const u32 b = sbid[e];
     if (e != 0 && sbid[e - 1] == b) return;
     u32 lo = e + 1, hi = n;  // one past the block's last point
@@ -722,63 +767,18 @@ static __global__ void __launch_bounds__(256)
     t.bcnt[b] += lo - e;
     atomicAdd(&t.ctr->npoints, (unsigned long long)(lo - e));
 }
-// One warp per touched cell: appends the cell's batch points to its chain. The head row is the
-// newest and the only partially filled one; new rows are linked in front of it.
 static __global__ void __launch_bounds__(256)
-    k_trees_append(TreesDev t, const u32* __restrict__ sslot, const u32* __restrict__ sidx, u32 n, const u32* __restrict__ seg_start,
-                   const float4* __restrict__ acc)
+    k_trees_write(TreesDev t, const u32* __restrict__ sidx, const u32* __restrict__ cslot, const u32* __restrict__ ord, u32 n,
+                  const float4* __restrict__ acc, const uint4* __restrict__ cwork)
 {
-    const int lane   = lane_id();
-    const u32 nwarps = (gridDim.x * blockDim.x) >> 5;
-    const u32 nseg   = t.ctr->nseg;
-    for (u32 s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < nseg; s += nwarps)
-    {
-        const u32 j0   = seg_start[s];
-        const u32 slot = sslot[j0];
-        Entry*    e    = t.ctab + slot;
-        u32       cnt  = e->cnt;
-        u32       head = e->vid;
-        if (cnt == 0)
-        {  // first points of this cell: publish it in the occupancy masks
-            head = VID_INVALID;
-            if (lane == 0)
-            {
-                const u32 bid = (u32)(e->key >> 15), cell = (u32)(e->key & (TR_CELLS - 1));
-                atomicOr(&t.l0[(size_t)bid * 1024 + (cell >> 5)], 1u << (cell & 31));
-                atomicOr(&t.l1[(size_t)bid * 16 + (cell >> 11)], 1u << ((cell >> 6) & 31));
-            }
-        }
-        u32 j = j0;
-        for (;;)
-        {
-            // room in the head row
-            u32 fill = cnt & (TR_ROW - 1);
-            if (fill == 0)
-            {  // head row full (or no row yet): link a new one in front
-                u32 row = 0;
-                if (lane == 0)
-                {
-                    row          = trees_alloc(&t.ctr->cfree_n, &t.ctr->crow_hi, t.cfree);
-                    t.cnext[row] = head;
-                }
-                head = __shfl_sync(MMG_FULL, row, 0);
-            }
-            const u32  room = TR_ROW - fill;
-            const u32  jj   = j + lane;
-            const bool take = (u32)lane < room && jj < n && sslot[jj] == slot;
-            if (take) t.cpts[(size_t)head * TR_ROW + fill + lane] = acc[sidx[jj]];
-            const u32 took = __popc(__ballot_sync(MMG_FULL, take));
-            cnt += took;
-            j += took;
-            if (took < room) break;                      // segment exhausted
-            if (!(j < n && sslot[j] == slot)) break;     // exactly filled the row and nothing is left
-        }
-        if (lane == 0)
-        {
-            e->vid = head;
-            e->cnt = cnt;
-        }
-    }
+    pdl_trigger();
+    pdl_wait();
+    const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    const uint4 w = cwork[cslot[e]];  // {old count, old head, first new row, 0}
+    const u32   g = w.x + ord[e], row_ord = g / TR_ROW, have = (w.x + TR_ROW - 1) / TR_ROW;
+    const u32   row = row_ord < have ? w.y : w.z + (row_ord - have);
+    t.cpts[(size_t)row * TR_ROW + (g & (TR_ROW - 1))] = acc[sidx[e]];
 }
 
 // ---------------------------------------------------------------- upkeep
