@@ -611,7 +611,8 @@ def run_config(args, rank, world, local_rank):
                     scaling="strong", config={"workload": "C4: " + out["workload"], "stored_points": out["stored_points"], "blocks": out["blocks"],
                                               "map_scans": out["scans"]},
                     result_stream_gbs=24.0 * head["hits"] / (head["ms"] * 1e-3) / 1e9, sweep=out["sweep"],
-                    insert={"mpts_s": out["insert_mpts_s"], "points_in": out["points_in"], "s": out["insert_s"]}, bcast_s=out["bcast_s"],
+                    insert={"mpts_s": out["insert_mpts_s"], "points_in": out["points_in"], "s": out["insert_s"], "ms_per_scan": out.get("insert_ms_per_scan")},
+                    bcast_s=out["bcast_s"],
                     nn_single_qps=out["nn_single_qps"], cpu_baseline=out.get("cpu"))
     else:
         line = dict(base, metric="nn_single_search queries/s (64 OS1-128 scans against the replicated map)", value=out["query_qps"], unit="queries/s",

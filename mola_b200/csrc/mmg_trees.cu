@@ -135,8 +135,10 @@ int rehash_ctab(mmg_map* m, u64 cap, cudaStream_t st)
 }
 int ensure_ctab(mmg_map* m, u64 entries, cudaStream_t st)
 {
-    const u64 cap = pow2_for(entries, 4096);
-    return cap <= m->trees->ccap ? MMG_OK : rehash_ctab(m, cap, st);
+    // a rehash costs two allocations, two host round trips and a pass over the old table: start at 2^18 slots (4 MB) and
+    // quadruple, so that a map build of millions of cells rehashes a handful of times
+    const u64 cap = pow2_for(entries, 1ull << 18);
+    return cap <= m->trees->ccap ? MMG_OK : rehash_ctab(m, m->trees->ccap ? 2 * cap : cap, st);
 }
 void set_grid(mmg_map* m)
 {  // setGridProperties, SparseTreesPointCloud.cpp:176-189

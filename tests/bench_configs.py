@@ -186,6 +186,7 @@ def run_c4(ctx):
     g = SparseTreesPointCloud(10.0, device=ctx.local_rank)
     g.insertionOptions.minimum_points_clearance = 0.05
     build_s, nscans, n_in = 0.0, 0, 0
+    per_scan = []
     if ctx.rank == 0:
         while nscans < a.c4_max_scans:  # the insert alone is timed (CUDA events); scan synthesis and the H2D copy are not
             xs, ys, zs, pose = synth.lidar_scan("hdl64", s=a.c4_spacing * nscans, seed=4, scan_id=nscans)
@@ -195,7 +196,8 @@ def run_c4(ctx):
             g.insertPointCloud(d[0], d[1], d[2], pose)
             e1.record(ctx.stream)
             e1.synchronize()
-            build_s += 1e-3 * e0.elapsed_time(e1)
+            per_scan.append(e0.elapsed_time(e1))
+            build_s += 1e-3 * per_scan[-1]
             n_in += xs.size
             nscans += 1
             if nscans % 32 == 0 and g.numPoints() >= a.c4_points:
@@ -241,7 +243,9 @@ def run_c4(ctx):
         return None
     out = {"config": "c4", "workload": f"SparseTreesPointCloud grid 10 m, clearance 0.05: nn_radius_search sweep, {nq_total} queries sharded x{ctx.world}",
            "n_gpus": ctx.world, "stored_points": int(g.numPoints()), "blocks": int(g.numVoxels()), "scans": nscans, "points_in": n_in,
-           "insert_s": build_s, "insert_mpts_s": n_in / build_s / 1e6 if build_s else None, "bcast_s": bcast_s, "nn_single_ms": nn_ms,
+           "insert_s": build_s, "insert_mpts_s": n_in / build_s / 1e6 if build_s else None,
+           "insert_ms_per_scan": {"median": float(np.median(per_scan)), "p90": float(np.percentile(per_scan, 90)), "max": float(np.max(per_scan)),
+                                  "top10_sum": float(np.sort(per_scan)[-10:].sum())} if per_scan else None, "bcast_s": bcast_s, "nn_single_ms": nn_ms,
            "nn_single_qps": nq_total / nn_ms * 1e3, "sweep": sweep}
     # CPU parity + baseline on a reduced twin (the reference's per-block kd-tree rebuild makes a 50M-pt CPU build impractical here)
     if a.c4_cpu_scans > 0:
