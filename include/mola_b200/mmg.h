@@ -152,6 +152,20 @@ int mmg_nn_single_batch(const mmg_map* m, const float* xs, const float* ys, cons
                         size_t n, const double* pose12, uint8_t* out_found, float* out_xyz,
                         float* out_d2, uint64_t* out_id, int mem, void* stream);
 
+/* nn_single_search for callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc. This entry point has NO counterpart in the reference.
+ * Same results as mmg_nn_single_batch (same kernels), but the pipeline's work area is a static __device__ array
+ * of the library (8 MiB + 256 B that every GPU loading the library holds until exit) instead of pool memory, and the call
+ * allocates nothing: no cudaMalloc / cudaFree / cudaMallocAsync, no allocating library routine.
+ *   - inputs and outputs are DEVICE buffers (there is no `mem` argument); HashedVoxel / SparseVoxel maps only
+ *   - n <= MMG_NOALLOC_MAX_QUERIES, else MMG_ERR_INVALID_ARG with a message naming the limit (split the batch)
+ *   - every call on a device shares the one array: calls that OVERLAP on the GPU (different streams) race on it;
+ *     calls issued on one stream are ordered and safe. */
+#define MMG_NOALLOC_MAX_QUERIES 65536
+int mmg_nn_single_batch_noalloc(const mmg_map* m, const float* xs, const float* ys, const float* zs,
+                                size_t n, const double* pose12, uint8_t* out_found, float* out_xyz,
+                                float* out_d2, uint64_t* out_id, void* stream);
+
 /* k nearest per query, k>=1. out_count[n] = matches written for that query
  * (<= min(k, map hard limit)); results of query i start at i*k. */
 int mmg_nn_multi_batch(const mmg_map* m, const float* xs, const float* ys, const float* zs,

@@ -47,7 +47,7 @@ class MmgError(RuntimeError):
 EXPORTS = [
     "mmg_default_params", "mmg_create", "mmg_destroy", "mmg_clear", "mmg_clone", "mmg_set_params",
     "mmg_get_params", "mmg_reserve", "mmg_insert_batch", "mmg_insert_scans", "mmg_nn_single_batch", "mmg_nn_multi_batch",
-    "mmg_nn_radius_batch", "mmg_nn_radius_fetch", "mmg_match_batch", "mmg_match_planes_batch", "mmg_likelihood", "mmg_bbox", "mmg_is_empty", "mmg_invalidate_bbox",
+    "mmg_nn_radius_batch", "mmg_nn_radius_fetch", "mmg_match_batch", "mmg_match_planes_batch", "mmg_nn_single_batch_noalloc", "mmg_likelihood", "mmg_bbox", "mmg_is_empty", "mmg_invalidate_bbox",
     "mmg_num_voxels", "mmg_num_points", "mmg_row_capacity", "mmg_export", "mmg_voxel_stats",
     "mmg_get_table_stats", "mmg_mean_stencil_points", "mmg_comm_unique_id", "mmg_comm_init", "mmg_comm_destroy", "mmg_bcast",
     "mmg_kernel_launch_count", "mmg_last_error", "mmg_version", "mmg_set_tuning",
