@@ -5,8 +5,12 @@
 #include "mmg_hits.cuh"
 #include "mmg_trees.cuh"
 #include "mmg_trees_radius.cuh"
+#include "mmg_vm.h"
 
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 using namespace mmg;
@@ -22,15 +26,51 @@ struct TreesState
     TreesCounters* h_ctr   = nullptr;  // pinned mirror
     uint4*         cwork = nullptr;  // one work word set per cell-table slot (k_trees_assign / k_trees_rows), sized like ctab
     u64            cwork_cap = 0;
-    cudaStream_t   pending_stream = nullptr;  // stream of the insert whose counters are still on their way (m->ctr_pending)
+    cudaStream_t   pending_stream = nullptr;
+    VmArray        vm[8];            // bkey, bcnt, l1, l0, bfree, cpts, cnext, cfree when they live in mapped virtual ranges
+    bool           use_vm = false;
+    size_t         vm_limit = 0;     // address space reserved per array  // stream of the insert whose counters are still on their way (m->ctr_pending)
 };
 }  // namespace mmg
 
 namespace
 {
-template <typename T>
-int grow(T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
+// MMG_TREES_TRACE=1: one stderr line per growth event (what grew, to what size, host time)
+struct GrowTrace
 {
+    const char* what;
+    u64         n;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    GrowTrace(const char* w, u64 n_) : what(w), n(n_) {}
+    ~GrowTrace()
+    {
+        static const bool on = getenv("MMG_TREES_TRACE") != nullptr;
+        if (on) fprintf(stderr, "[trees] grow %s -> %llu: %.3f ms\n", what, (unsigned long long)n, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    }
+};
+// Grows a device array to newn elements, new elements filled with fill_byte. Preferred: physical memory mapped behind
+// a virtual range reserved once (mmg_vm.h) - the old contents stay where they are, nothing is copied or freed, the stream is
+// not synchronised and kernels in flight keep valid pointers. Without the driver API (or MMG_NO_VM=1): allocate, copy, free.
+template <typename T>
+int grow(mmg_map* m, int slot, T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
+{
+    TreesState* s = m->trees;
+    VmArray&    a = s->vm[slot];
+    if (s->use_vm && !a.base && !*p)
+    {   // first allocation of this array: reserve address space for anything the device could hold
+        if (vm_reserve(a, s->vm_limit, m->device) != 0) a = VmArray();
+    }
+    if (a.base)
+    {
+        if (vm_ensure(a, newn * sizeof(T)) != 0)
+        {
+            set_error("mapping %llu B of device memory failed", (unsigned long long)(newn * sizeof(T)));
+            return MMG_ERR_OUT_OF_MEM;
+        }
+        *p = reinterpret_cast<T*>(a.base);
+        MMG_CUDA(cudaMemsetAsync(*p + oldn, fill_byte, (newn - oldn) * sizeof(T), st));
+        return MMG_OK;
+    }
     T* q = nullptr;
     if (cudaMalloc(&q, newn * sizeof(T)) != cudaSuccess)
     {
@@ -44,6 +84,14 @@ int grow(T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
     if (*p) cudaFree(*p);
     *p = q;
     return MMG_OK;
+}
+template <typename T>
+void release(mmg_map* m, int slot, T** p)
+{
+    VmArray& a = m->trees->vm[slot];
+    if (a.base) vm_release(a);
+    else if (*p) cudaFree(*p);
+    *p = nullptr;
 }
 int new_table(Entry** tab, u64 cap)
 {
@@ -79,11 +127,12 @@ int ensure_block_rows(mmg_map* m, u64 rows, cudaStream_t st)
     if (rows <= s->brows) return MMG_OK;
     const u64 nc = std::max<u64>(rows + rows / 2, 256);
     int       rc;
-    if ((rc = grow(&s->dev.bkey, s->brows, nc, 0xFF, st))) return rc;
-    if ((rc = grow(&s->dev.bcnt, s->brows, nc, 0, st))) return rc;
-    if ((rc = grow(&s->dev.l1, s->brows * 16, nc * 16, 0, st))) return rc;
-    if ((rc = grow(&s->dev.l0, s->brows * 1024, nc * 1024, 0, st))) return rc;
-    if ((rc = grow(&s->dev.bfree, s->brows, nc, 0, st))) return rc;
+    GrowTrace tr("block rows", nc);
+    if ((rc = grow(m, 0, &s->dev.bkey, s->brows, nc, 0xFF, st))) return rc;
+    if ((rc = grow(m, 1, &s->dev.bcnt, s->brows, nc, 0, st))) return rc;
+    if ((rc = grow(m, 2, &s->dev.l1, s->brows * 16, nc * 16, 0, st))) return rc;
+    if ((rc = grow(m, 3, &s->dev.l0, s->brows * 1024, nc * 1024, 0, st))) return rc;
+    if ((rc = grow(m, 4, &s->dev.bfree, s->brows, nc, 0, st))) return rc;
     s->brows = nc;
     return MMG_OK;
 }
@@ -91,11 +140,12 @@ int ensure_chain_rows(mmg_map* m, u64 rows, cudaStream_t st)
 {
     TreesState* s = m->trees;
     if (rows <= s->crows) return MMG_OK;
-    const u64 nc = std::max<u64>(2 * rows, 65536);  // 32 MB of rows at least, doubling: a map build sees a handful of copies
+    const u64 nc = std::max<u64>(2 * rows, 65536);  // 32 MB of rows at least, doubling
     int       rc;
-    if ((rc = grow(&s->dev.cpts, s->crows * TR_ROW, nc * TR_ROW, 0, st))) return rc;
-    if ((rc = grow(&s->dev.cnext, s->crows, nc, 0xFF, st))) return rc;
-    if ((rc = grow(&s->dev.cfree, s->crows, nc, 0, st))) return rc;
+    GrowTrace tr("chain rows", nc);
+    if ((rc = grow(m, 5, &s->dev.cpts, s->crows * TR_ROW, nc * TR_ROW, 0, st))) return rc;
+    if ((rc = grow(m, 6, &s->dev.cnext, s->crows, nc, 0xFF, st))) return rc;
+    if ((rc = grow(m, 7, &s->dev.cfree, s->crows, nc, 0, st))) return rc;
     s->crows = nc;
     return MMG_OK;
 }
@@ -105,6 +155,7 @@ int ensure_btab(mmg_map* m, u64 entries, cudaStream_t st)
     TreesState* s   = m->trees;
     const u64   cap = pow2_for(entries, 1024);
     if (cap <= s->bcap) return MMG_OK;
+    GrowTrace tr("block table", cap);
     MMG_CUDA(cudaStreamSynchronize(st));
     Entry* t  = nullptr;
     int    rc = new_table(&t, cap);
@@ -118,6 +169,7 @@ int ensure_btab(mmg_map* m, u64 entries, cudaStream_t st)
 int rehash_ctab(mmg_map* m, u64 cap, cudaStream_t st)
 {
     TreesState* s = m->trees;
+    GrowTrace   tr("cell table", cap);
     MMG_CUDA(cudaStreamSynchronize(st));
     Entry*    old    = s->dev.ctab;
     const u64 oldcap = s->ccap;
@@ -157,6 +209,12 @@ int trees_create(mmg_map* m)
     MMG_CUDA(cudaMalloc(&s->dev.ctr, sizeof(TreesCounters)));
     MMG_CUDA(cudaMemset(s->dev.ctr, 0, sizeof(TreesCounters)));
     MMG_CUDA(cudaMallocHost(&s->h_ctr, sizeof(TreesCounters)));
+    {
+        static const bool no_vm = getenv("MMG_NO_VM") != nullptr;
+        size_t            fr = 0, tot = 0;
+        s->use_vm   = !no_vm && vm_available() && cudaMemGetInfo(&fr, &tot) == cudaSuccess;
+        s->vm_limit = tot;
+    }
     set_grid(m);
     int rc = ensure_btab(m, 256, 0);
     if (!rc) rc = ensure_ctab(m, 1024, 0);
@@ -166,8 +224,10 @@ int trees_destroy(mmg_map* m)
 {
     TreesState* s = m->trees;
     if (!s) return MMG_OK;
-    cudaFree(s->dev.btab), cudaFree(s->dev.bkey), cudaFree(s->dev.bcnt), cudaFree(s->dev.l1), cudaFree(s->dev.l0), cudaFree(s->dev.bfree);
-    cudaFree(s->dev.ctab), cudaFree(s->dev.cpts), cudaFree(s->dev.cnext), cudaFree(s->dev.cfree), cudaFree(s->dev.ctr);
+    cudaDeviceSynchronize();  // unmapping does not wait for kernels the way cudaFree does
+    cudaFree(s->dev.btab), cudaFree(s->dev.ctab), cudaFree(s->dev.ctr);
+    release(m, 0, &s->dev.bkey), release(m, 1, &s->dev.bcnt), release(m, 2, &s->dev.l1), release(m, 3, &s->dev.l0), release(m, 4, &s->dev.bfree);
+    release(m, 5, &s->dev.cpts), release(m, 6, &s->dev.cnext), release(m, 7, &s->dev.cfree);
     if (s->cwork) cudaFree(s->cwork);
     if (s->h_ctr) cudaFreeHost(s->h_ctr);
     delete s;
@@ -348,7 +408,9 @@ int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, 
         if ((rc = ensure_ctab(m, (u64)s->ncells + nacc, st))) return rc;
         if ((rc = ensure_chain_rows(m, (u64)s->crow_hi + nacc + nacc / TR_ROW + 2, st))) return rc;
         if (s->cwork_cap != s->ccap)
-        {   // per-slot work words of the cell table (batch ordinals, then the owner's row bookkeeping); all zero between batches
+        {
+            GrowTrace tr("cell work words", s->ccap);
+            // per-slot work words of the cell table (batch ordinals, then the owner's row bookkeeping); all zero between batches
             MMG_CUDA(cudaStreamSynchronize(st));
             if (s->cwork) cudaFree(s->cwork);
             s->cwork = nullptr, s->cwork_cap = 0;
