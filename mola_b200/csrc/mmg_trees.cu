@@ -58,7 +58,9 @@ int grow(mmg_map* m, int slot, T** p, u64 oldn, u64 newn, int fill_byte, cudaStr
     VmArray&    a = s->vm[slot];
     if (s->use_vm && !a.base && !*p)
     {   // first allocation of this array: reserve address space for anything the device could hold
-        if (vm_reserve(a, s->vm_limit, m->device) != 0) a = VmArray();
+        // (bytes per row relative to the largest array of its group: l0 = 4 KB per block row, cpts = 512 B per chain row)
+        static const size_t div[8] = {512, 1024, 64, 1, 1024, 1, 128, 128};
+        if (vm_reserve(a, s->vm_limit / div[slot] + (size_t(64) << 20), m->device) != 0) a = VmArray();
     }
     if (a.base)
     {

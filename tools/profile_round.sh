@@ -18,4 +18,10 @@ ncu --set full --clock-control none --import-source on -k regex:k_insert_rank -s
 ncu --set full --clock-control none --import-source on -k regex:k_insert_commit -s 2 -c 2 -o gpurun_out/${T}_prof_commit python bench.py --only insert_batched > gpurun_out/${T}_ncu4.log 2>&1
 # (compute-sanitizer is closed on this GPU pool: `compute-sanitizer --tool racecheck python tools/racecheck_insert.py` where it is open)
 fi
+# the other BASELINE configurations as bench lines (C4: 50 M-point SparseTrees radius sweep; C5: 64 OS1-128 scans inserted + queried)
+python bench.py --config c4 --no-cpu > gpurun_out/${T}_c4_n1.json 2> gpurun_out/${T}_c4_n1.err
+python bench.py --config c5 > gpurun_out/${T}_c5_n1.json 2> gpurun_out/${T}_c5_n1.err
+python tests/bench_configs.py --configs c1,c3 > gpurun_out/${T}_configs_c1_c3.jsonl 2> gpurun_out/${T}_configs.err
+AB_MATCH=1 python tools/nn_ab.py nn_kernel=0 > gpurun_out/${T}_match_rate.json 2> gpurun_out/${T}_match_rate.err
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/${T}_launches_c4_2Mpts.csv python bench.py --config c4 --c4-points 2000000 --no-cpu --steps 1 --warmup 1 > gpurun_out/${T}_ncu5.log 2>&1
 cut -c1-300 gpurun_out/${T}_bench_n1.json
