@@ -620,7 +620,9 @@ static int nn_single_voxel(const mmg_map* cm, const float* xs, const float* ys, 
             // batch into chunks that alternate between two streams did not make the stages of different chunks overlap:
             // 0.80 - 0.97 ms for chunks of 64k - 512k queries, profiles/r2f_*; queries copied in by DMA chunk by chunk on a
             // second stream with each chunk's kernel writing straight to the host buffers: 0.76 / 0.82 / 0.99 ms for 2 / 4 / 8
-            // chunks - every kernel boundary waits for its posted writes to drain)
+            // chunks - every kernel boundary waits for its posted writes to drain; queries read in place and the results
+            // copied out by DMA chunk by chunk: 0.74 / 0.76 / 0.82 ms - the kernels' read requests queue behind the result
+            // copy on the upstream lanes; copy engines both ways, 4 chunks on three streams: 0.71 ms)
             const int rc = launch_nn_single<Tr>(m, (const float*)dp[0], (const float*)dp[1], (const float*)dp[2], nq, 1, T, pose12 ? 1 : 0,
                                                 QueryOut{(uint8_t*)dp[3], (float*)dp[4], (float*)dp[5], (u64*)dp[6]}, st, bd_init, nullptr, true);
             if (rc) return rc;
