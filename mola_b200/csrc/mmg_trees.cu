@@ -388,14 +388,13 @@ int trees_insert(mmg_map* m, const float* xs, const float* ys, const float* zs, 
     {
         u32* todo = (u32*)m->scratch_get(S_TREES_TODO, (n + 1) * sizeof(u32));
         if (!todo) return MMG_ERR_OUT_OF_MEM;
-        MMG_CUDA(cudaMemsetAsync(todo + n, 0, sizeof(u32), st));
-        MMG_LAUNCH(k_trees_clear, gN, 256, 0, st, s->dev, dx, dy, dz, N, T, thr, gp, d2, todo, todo + n);
+        MMG_LAUNCH(k_trees_clear, (unsigned)(((u64)N * TRC_LANES + 255) / 256), 256, 0, st, s->dev, dx, dy, dz, N, T, thr, gp, d2, todo);
         // the points the 3x3x3 cell region could not decide (none at centimetre clearances): exact search
         const float* gq = (const float*)gp;
         MMG_LAUNCH(k_trees_nn1, persistent_blocks(m, n, 8, 8), 256, 0, st, s->dev, gq, gq + 1, gq + 2, N, 4u, T, 0, -1.0f, (uint8_t*)nullptr, (float*)nullptr,
-                   d2, (u64*)nullptr, (const u32*)todo, (const u32*)(todo + n));
+                   d2, (u64*)nullptr, (const u32*)todo, (const u32*)&s->dev.ctr->ntodo);
     }
-    MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->oob, 0, sizeof(u32), st));
+    if (no_clearance) MMG_CUDA(cudaMemsetAsync(&s->dev.ctr->oob, 0, sizeof(u32), st));  // (k_trees_clear does it otherwise)
     MMG_LAUNCH(k_trees_flags, gN, 256, 0, st, s->dev, gp, d2, N, thr, flag);
     exclusive_scan<u32, u32>(flag, pos, n, &s->dev.ctr->nacc, bsum, st);
     if ((rc = ensure_btab(m, (u64)(s->brow_hi - s->bfree_n) + n, st))) return rc;  // every kept point could open a block

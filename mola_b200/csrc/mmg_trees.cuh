@@ -38,7 +38,7 @@ struct TreesCounters
     u32 ncells;            // live cell entries
     u32 oob;
     u32 nseg;
-    u32 need_rows;         // (unused since the append reserves rows by an upper bound)
+    u32 ntodo;             // points k_trees_clear left to the exact search (zeroed again by k_trees_flags)
     u32 maxcnt;            // scratch for reductions
     u32 nacc;              // points the current batch keeps (total of the flag scan)
     unsigned long long npoints;
@@ -491,20 +491,27 @@ static __global__ void k_trees_compose(const float* __restrict__ xs, const float
     const float3 g = compose_point(pose, xs[i], ys[i], zs[i]);
     gp[i]          = make_float4(g.x, g.y, g.z, 0.f);
 }
-// Clearance test of phase 1 in one pass, one THREAD per input point: compose, then ask whether the pre-batch map holds
+// Clearance test of phase 1 in one pass, FOUR lanes per input point: compose, then ask whether the pre-batch map holds
 // ANY point of the same block with d2 <= thr (= the reference's "nearest neighbour has d2 <= clearance^2": the nearest
 // one is within thr iff some point is). Only the fine cells whose box can reach thr are opened, and the walk stops at
-// the first such point. Writes the composed point and d2 = that point's distance (<= thr: rejected by k_trees_flags)
-// or -1 ("none": kept). When thr reaches past the 3x3x3 cell region (clearance of the order of the 0.31 m cells) the
-// region cannot certify "none": those points go to `todo` for the exact search (k_trees_nn1).
+// the first row holding such a point. The four lanes walk the same cells and rows together and each looks at its own
+// eight slots of a 32-slot row (four 256-bit loads), so a row costs ONE load round trip (the
+// kernel is bound by the chain of dependent L2 round trips, not by bandwidth or issue). Writes the composed point and
+// d2 = some distance <= thr (rejected by k_trees_flags) or -1 ("none": kept). When thr reaches past the 3x3x3 cell region
+// (clearance of the order of the 0.31 m cells) the region cannot certify "none": those points go to `todo` for the
+// exact search (k_trees_nn1).
+constexpr int TRC_LANES = 4;
 static __global__ void __launch_bounds__(256)
     k_trees_clear(TreesDev t, const float* __restrict__ xs, const float* __restrict__ ys, const float* __restrict__ zs, u32 n, PoseD pose, float thr,
-                  float4* __restrict__ gp, float* __restrict__ d2, u32* __restrict__ todo, u32* __restrict__ ntodo)
+                  float4* __restrict__ gp, float* __restrict__ d2, u32* __restrict__ todo)
 {
-    const u32 q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= n) return;
-    const float3 p = compose_point(pose, xs[q], ys[q], zs[q]);
-    gp[q]          = make_float4(p.x, p.y, p.z, 0.f);
+    if (blockIdx.x == 0 && threadIdx.x == 0) t.ctr->oob = 0;  // counted by k_trees_flags, read by the host after k_trees_locate
+    const u32 q = (blockIdx.x * blockDim.x + threadIdx.x) / TRC_LANES;
+    if (q >= n) return;  // whole groups leave together (blockDim is a multiple of TRC_LANES)
+    const int      sub   = threadIdx.x & (TRC_LANES - 1);
+    const unsigned gmask = ((1u << TRC_LANES) - 1u) << (lane_id() & ~(TRC_LANES - 1));
+    const float3   p     = compose_point(pose, xs[q], ys[q], zs[q]);
+    if (sub == 0) gp[q] = make_float4(p.x, p.y, p.z, 0.f);
     int   kx, ky, kz;
     u32   bid = 0;
     float hit = -1.0f;
@@ -529,20 +536,21 @@ static __global__ void __launch_bounds__(256)
             u32 fill = ((cnt - 1) & (TR_ROW - 1)) + 1, row = head;
             for (u32 r = 0, nrows = (cnt + TR_ROW - 1) / TR_ROW; r < nrows && hit < 0.f; r++)
             {
-                const float4* rp  = t.cpts + (size_t)row * TR_ROW;
+                const float4* rp  = t.cpts + (size_t)row * TR_ROW + sub * 8;
                 const u32     nxt = (r + 1 < nrows) ? __ldg(&t.cnext[row]) : 0u;  // in flight together with the row
-                for (u32 s = 0; s < fill && hit < 0.f; s += 8)
-                {   // eight slots per step, four independent 256-bit loads (slots past `fill` are loaded but never looked at)
-                    float4 c[8];
+                float4        c[8];  // this lane's eight slots (slots past `fill` are loaded but never looked at)
 #pragma unroll
-                    for (int k = 0; k < 4; k++) ld_row_pair(rp + s + 2 * k, c[2 * k], c[2 * k + 1]);
+                for (int k = 0; k < 4; k++) ld_row_pair(rp + 2 * k, c[2 * k], c[2 * k + 1]);
+                float mine = -1.0f;
 #pragma unroll
-                    for (int k = 0; k < 8; k++)
-                    {
-                        const float d = sqr_dist(qv[0], qv[1], qv[2], c[k].x, c[k].y, c[k].z);
-                        if (s + k < fill && d <= thr && hit < 0.f) hit = d;
-                    }
+                for (int k = 0; k < 8; k++)
+                {
+                    const float d = sqr_dist(qv[0], qv[1], qv[2], c[k].x, c[k].y, c[k].z);
+                    if ((u32)(sub * 8 + k) < fill && d <= thr) mine = d;
                 }
+                // any lane's hit ends the walk for the group; every lane takes the hit of the lowest lane that has one
+                const unsigned any = __ballot_sync(gmask, mine >= 0.f) & gmask;
+                if (any) hit = __shfl_sync(gmask, mine, __ffs(any) - 1);
                 row  = nxt;
                 fill = TR_ROW;
             }
@@ -561,12 +569,14 @@ static __global__ void __launch_bounds__(256)
             sure = thr < out * out * 0.9999f;
         }
     }
+    if (sub != 0) return;
     if (sure) d2[q] = hit;
-    else todo[atomicAdd(ntodo, 1u)] = q;
+    else todo[atomicAdd(&t.ctr->ntodo, 1u)] = q;
 }
 static __global__ void k_trees_flags(TreesDev t, const float4* __restrict__ gp, const float* __restrict__ d2, u32 n, float thr, u32* __restrict__ flag)
 {
     const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) t.ctr->ntodo = 0;  // the exact search before this kernel has consumed the list: ready for the next batch
     if (i >= n) return;
     const float4 p = gp[i];
     int          kx, ky, kz;

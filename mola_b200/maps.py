@@ -76,6 +76,11 @@ class _Map:
         raise NotImplementedError
 
     def _sync_params(self):
+        # fast path (every insert / query call comes through here): nothing to do while the option values are the same objects
+        key = (*vars(self.insertionOptions).values(), *vars(self.likelihoodOptions).values())
+        if key == getattr(self, "_opt_key", None):
+            return
+        self._opt_key = key
         p = capi.Params.from_buffer_copy(self._p)
         lo = self.likelihoodOptions
         p.sigma_dist, p.max_corr_distance, p.decimation = float(lo.sigma_dist), float(lo.max_corr_distance), int(lo.decimation)
