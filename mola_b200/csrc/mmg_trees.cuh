@@ -585,14 +585,25 @@ static __global__ void k_trees_flags(TreesDev t, const float4* __restrict__ gp, 
     const float d = d2[i];
     flag[i]       = (ok && (d < 0.f || d > thr)) ? 1u : 0u;
 }
+// Extends the bounding box (ordered-uint min xyz / max xyz) by the warp's valid points. The current box is read first
+// (a stale copy is only ever smaller): only warps holding a point outside it reduce and issue atomics - none in steady state.
 __device__ __forceinline__ void warp_bbox6(u32* bbox, bool ok, float x, float y, float z)
 {
     const float v[3] = {x, y, z};
+    u32         o[3];
+    bool        ext = false;
 #pragma unroll
     for (int a = 0; a < 3; a++)
     {
-        const u32 mn = __reduce_min_sync(MMG_FULL, ok ? float_to_ordered(v[a]) : 0xFFFFFFFFu);
-        const u32 mx = __reduce_max_sync(MMG_FULL, ok ? float_to_ordered(v[a]) : 0u);
+        o[a] = float_to_ordered(v[a]);
+        ext |= ok && (o[a] < __ldcg(&bbox[a]) || o[a] > __ldcg(&bbox[3 + a]));
+    }
+    if (!__any_sync(MMG_FULL, ext)) return;
+#pragma unroll
+    for (int a = 0; a < 3; a++)
+    {
+        const u32 mn = __reduce_min_sync(MMG_FULL, ok ? o[a] : 0xFFFFFFFFu);
+        const u32 mx = __reduce_max_sync(MMG_FULL, ok ? o[a] : 0u);
         if (lane_id() == 0)
         {
             if (mn != 0xFFFFFFFFu) atomicMin(&bbox[a], mn);
