@@ -202,9 +202,33 @@ static int ensure_table(mmg_map* m, u64 entries, cudaStream_t st)
     return MMG_OK;
 }
 
+// Grows a row array to newn elements, new elements filled with fill_byte. Preferred: physical memory mapped behind a
+// virtual range reserved once (mmg_vm.h): nothing is copied or freed, the stream is not synchronised, kernels in flight keep
+// valid pointers. Without the driver API (or MMG_NO_VM=1): allocate, copy, free.
 template <typename T>
-static int grow_array(T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
+static int grow_array(mmg_map* m, int slot, T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
 {
+    VmArray& a = m->vm[slot];
+    // (a first allocation of a gigabyte or more - the worst-case headroom of a multi-million-point batch into a new map -
+    // stays with cudaMalloc: mapping page by page costs up to 3 x more there, and a store born that large rarely grows again)
+    // Only the point rows (slot 0: 512 B per row, 98 % of the bytes) live in a mapped range: the small arrays copy a few MB
+    // when they grow, which is cheaper than a reservation + mapping each (1.5 ms apiece on a new map).
+    if (m->use_vm && slot == 0 && !a.base && !*p && newn * sizeof(T) < (size_t(1) << 30))
+    {   // address space for anything the device could hold (bytes per row relative to the point rows)
+        static const size_t div[6] = {1, 128, 64, 128, 128, 32};
+        if (vm_reserve(a, m->vm_limit / div[slot] + (size_t(64) << 20), m->device) != 0) a = VmArray();
+    }
+    if (a.base)
+    {
+        if (vm_ensure(a, newn * sizeof(T)) != 0)
+        {
+            set_error("mapping %llu B of device memory failed", (unsigned long long)(newn * sizeof(T)));
+            return MMG_ERR_OUT_OF_MEM;
+        }
+        *p = reinterpret_cast<T*>(a.base);
+        MMG_CUDA(cudaMemsetAsync(*p + oldn, fill_byte, (newn - oldn) * sizeof(T), st));
+        return MMG_OK;
+    }
     T* q = nullptr;
     if (cudaMalloc(&q, newn * sizeof(T)) != cudaSuccess)
     {
@@ -222,6 +246,13 @@ static int grow_array(T** p, u64 oldn, u64 newn, int fill_byte, cudaStream_t st)
     *p = q;
     return MMG_OK;
 }
+template <typename T>
+static void release_array(mmg_map* m, int slot, T** p)
+{
+    if (m->vm[slot].base) vm_release(m->vm[slot]);
+    else if (*p) cudaFree(*p);
+    *p = nullptr;
+}
 
 int mmg::ensure_rows(mmg_map* m, u64 rows, cudaStream_t st)
 {
@@ -232,12 +263,12 @@ int mmg::ensure_rows(mmg_map* m, u64 rows, cudaStream_t st)
     const u64 newcap = std::max<u64>(2 * rows, (u64)1 << 18);
     const u64 cap_pts = (u64)m->row_points();
     int       rc;
-    if ((rc = grow_array(&m->dev.pts, m->rowcap * cap_pts, newcap * cap_pts, 0, st))) return rc;
-    if ((rc = grow_array(&m->dev.cnt, m->rowcap, newcap, 0, st))) return rc;
-    if ((rc = grow_array(&m->dev.vkey, m->rowcap, newcap, 0xFF, st))) return rc;
-    if ((rc = grow_array(&m->dev.free_list, m->rowcap, newcap, 0, st))) return rc;
-    if ((rc = grow_array(&m->dev.fill, m->rowcap, newcap, 0, st))) return rc;
-    if (m->kind == MMG_SPARSE_VOXEL && (rc = grow_array(&m->dev.mean, m->rowcap, newcap, 0, st))) return rc;
+    if ((rc = grow_array(m, 0, &m->dev.pts, m->rowcap * cap_pts, newcap * cap_pts, 0, st))) return rc;
+    if ((rc = grow_array(m, 1, &m->dev.cnt, m->rowcap, newcap, 0, st))) return rc;
+    if ((rc = grow_array(m, 2, &m->dev.vkey, m->rowcap, newcap, 0xFF, st))) return rc;
+    if ((rc = grow_array(m, 3, &m->dev.free_list, m->rowcap, newcap, 0, st))) return rc;
+    if ((rc = grow_array(m, 4, &m->dev.fill, m->rowcap, newcap, 0, st))) return rc;
+    if (m->kind == MMG_SPARSE_VOXEL && (rc = grow_array(m, 5, &m->dev.mean, m->rowcap, newcap, 0, st))) return rc;
     m->rowcap = newcap;
     return MMG_OK;
 }
@@ -946,6 +977,12 @@ int mmg_create(int kind, const mmg_params* p, int device, mmg_map** out)
         if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
         cudaGetLastError();
     }
+    {
+        static const bool no_vm = getenv("MMG_NO_VM") != nullptr;
+        size_t            fr = 0, tot = 0;
+        m->use_vm   = !no_vm && vm_available() && cudaMemGetInfo(&fr, &tot) == cudaSuccess;
+        m->vm_limit = tot;
+    }
     int rc = init_counters(m, false);
     if (!rc && kind != MMG_SPARSE_TREES) rc = alloc_table(m, 1u << 16, 0);
     cudaStreamSynchronize(0);  // the table is usable from any stream once mmg_create returns
@@ -965,8 +1002,9 @@ int mmg_destroy(mmg_map* m)
     cudaSetDevice(m->device);
     cudaDeviceSynchronize();
     if (m->kind == MMG_SPARSE_TREES) trees_destroy(m);
-    cudaFree(m->dev.table), cudaFree(m->dev.pts), cudaFree(m->dev.cnt), cudaFree(m->dev.vkey), cudaFree(m->dev.mean), cudaFree(m->dev.free_list), cudaFree(m->dev.fill),
-        cudaFree(m->dev.ctr);
+    cudaFree(m->dev.table), cudaFree(m->dev.ctr);
+    release_array(m, 0, &m->dev.pts), release_array(m, 1, &m->dev.cnt), release_array(m, 2, &m->dev.vkey), release_array(m, 3, &m->dev.free_list);
+    release_array(m, 4, &m->dev.fill), release_array(m, 5, &m->dev.mean);
     if (m->h_ctr) cudaFreeHost(m->h_ctr);
     if (m->ev_ctr) cudaEventDestroy(m->ev_ctr);
     if (m->h_stage) cudaFreeHost(m->h_stage);

@@ -9,6 +9,7 @@
 
 #include "../../include/mola_b200/mmg.h"
 #include "mmg_voxel.cuh"
+#include "mmg_vm.h"
 
 namespace mmg
 {
@@ -108,6 +109,10 @@ struct mmg_map
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t  ev_start = nullptr, ev_in[8] = {}, ev_k[8] = {};
     int          ensure_pipeline();
+    // row arrays (pts, cnt, vkey, free_list, fill, mean) that grow in place behind reserved virtual ranges (mmg_vm.h)
+    mmg::VmArray vm[6];
+    bool         use_vm   = false;
+    size_t       vm_limit = 0;
     std::mutex   pipe_mtx;  // the pageable-host-buffer pipeline (streams + events above) serves one call at a time
     // grow-only device scratch
     std::vector<std::pair<void*, size_t>> scratch;

@@ -211,12 +211,7 @@ int trees_create(mmg_map* m)
     MMG_CUDA(cudaMalloc(&s->dev.ctr, sizeof(TreesCounters)));
     MMG_CUDA(cudaMemset(s->dev.ctr, 0, sizeof(TreesCounters)));
     MMG_CUDA(cudaMallocHost(&s->h_ctr, sizeof(TreesCounters)));
-    {
-        static const bool no_vm = getenv("MMG_NO_VM") != nullptr;
-        size_t            fr = 0, tot = 0;
-        s->use_vm   = !no_vm && vm_available() && cudaMemGetInfo(&fr, &tot) == cudaSuccess;
-        s->vm_limit = tot;
-    }
+    s->use_vm = m->use_vm, s->vm_limit = m->vm_limit;  // decided once per map in mmg_create
     set_grid(m);
     int rc = ensure_btab(m, 256, 0);
     if (!rc) rc = ensure_ctab(m, 1024, 0);
