@@ -20,7 +20,7 @@
 namespace mmg
 {
 std::atomic<unsigned long long> g_launches{0};
-int                       g_tune[T_COUNT] = {0, 16, 4096, 1, 1 << 26, 0x7FFFFFFF, 6, 2048, 6144, 1};
+int                       g_tune[T_COUNT] = {0, 16, 4096, 1, 1 << 26, 0x7FFFFFFF, 6, 2048, 6144, 1, 1};
 static thread_local char  g_err[512] = "";
 void set_error(const char* fmt, ...)
 {
@@ -1591,7 +1591,7 @@ int mmg_mean_stencil_points(const mmg_map* cm, const float* xs, const float* ys,
 
 int mmg_set_tuning(const char* key, int value)
 {
-    static const char* names[T_COUNT] = {"nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute", "radius_chunk_hits", "sv_split_hits", "nn_task_minb", "radius_warp_max", "radius_block_mid", "radius_q16"};
+    static const char* names[T_COUNT] = {"nn_kernel", "nn_task_blocks", "nn_min_pipe", "nn_permute", "radius_chunk_hits", "sv_split_hits", "nn_task_minb", "radius_warp_max", "radius_block_mid", "radius_q16", "radius_topk"};
     for (int i = 0; key && i < T_COUNT; i++)
         if (!strcmp(key, names[i]))
         {

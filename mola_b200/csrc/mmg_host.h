@@ -160,6 +160,7 @@ enum Tune
     T_RADIUS_WARP_MAX,    // SparseTrees radius search: lists up to this many hits are sorted by a warp, longer ones by a block
     T_RADIUS_BLOCK_MID,   // SparseTrees radius search: lists up to this many hits share an SM three blocks at a time
     T_RADIUS_Q16,         // SparseTrees radius search: sort on the 16-bit monotone image of d2 (1) or on the raw key bits (0)
+    T_RADIUS_TOPK,        // SparseTrees radius search with maxPoints <= 32: per-block bounded k-nearest search (1) or the hit-list path (0)
     T_COUNT
 };
 extern int g_tune[T_COUNT];

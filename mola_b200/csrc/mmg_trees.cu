@@ -560,6 +560,43 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
         const PoseD    T  = make_pose(pose12);
         const unsigned nb = persistent_blocks(m, n, 8, 8);
         MMG_CUDA(cudaMemsetAsync(next, 0, 4 * sizeof(u32) + sizeof(TreesRadiusErr), st));
+        const u64 stride = nbq * (u64)maxp;
+        if (maxp >= 1 && maxp <= 32 && stride <= TRK_CAP && (u64)n * stride * 24 <= ((u64)2 << 30) && g_tune[T_RADIUS_TOPK])
+        {   // small maxPoints: per-block bounded k-nearest search, no hit list (mmg_trees_radius.cuh, k_trees_radius_topk)
+            char* hb = (char*)m->scratch_get(S_RHITS, (u64)n * stride * 24);
+            if (!hb) return MMG_ERR_OUT_OF_MEM;
+            u64*   rid    = (u64*)hb;
+            float* rxyz   = (float*)(hb + (u64)n * stride * 8);
+            float* rd2    = (float*)(hb + (u64)n * stride * 20);
+            u32*   outcnt = bound;
+            MMG_LAUNCH(k_trees_radius_topk, (unsigned)std::min<size_t>((n + TRK_WARPS - 1) / TRK_WARPS, (size_t)m->num_sms * 16), TRK_WARPS * 32, 0, st, s->dev,
+                       dx, dy, dz, (u32)n, T, pose12 ? 1 : 0, r2, r, maxp, (u32)stride, rxyz, rd2, rid, outcnt, derr);
+            MMG_LAUNCH(k_trees_radius_stride_offsets, (unsigned)((n + 256) / 256), 256, 0, st, (u32)n, (u32)stride, boff);
+            exclusive_scan<u32, u64>(outcnt, noff, n, noff + n, noff + n + 1, st);
+            u64            tot = 0;
+            TreesRadiusErr herr;
+            MMG_CUDA(cudaMemcpyAsync(&tot, noff + n, sizeof(u64), cudaMemcpyDeviceToHost, st));
+            MMG_CUDA(cudaMemcpyAsync(&herr, derr, sizeof(herr), cudaMemcpyDeviceToHost, st));
+            MMG_CUDA(cudaStreamSynchronize(st));
+            if (herr.rank_overflow)
+            {
+                set_error("nn_radius_search: the blocks around a query hold more than 2^32 points");
+                return MMG_ERR_INVALID_ARG;
+            }
+            char* pb = (char*)m->scratch_get(S_RHITS2, std::max<u64>(tot, 1) * 24);
+            if (!pb) return MMG_ERR_OUT_OF_MEM;
+            u64*   pid  = (u64*)pb;
+            float* pxyz = (float*)(pb + tot * 8);
+            float* pd2  = (float*)(pb + tot * 20);
+            MMG_LAUNCH(k_trees_radius_pack, nb, 256, 0, st, (u32)n, (const u32*)outcnt, (const u64*)boff, (const u64*)noff, (const float*)rxyz,
+                       (const float*)rd2, (const u64*)rid, pxyz, pd2, pid);
+            rad_result().total = tot, rad_result().id = pid, rad_result().xyz = pxyz, rad_result().d2 = pd2;
+            MMG_CUDA(cudaGetLastError());
+            MMG_CUDA(cudaMemcpyAsync(ooff, noff, (n + 1) * sizeof(u64), mem == MMG_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+            MMG_CUDA(cudaStreamSynchronize(st));
+            if (ototal) *ototal = tot;
+            return MMG_OK;
+        }
         MMG_LAUNCH((k_trees_radius_hits<0>), nb, 256, 0, st, s->dev, dx, dy, dz, 0u, (u32)n, T, pose12 ? 1 : 0, r2, r, cnt, (const u64*)nullptr, 0ull,
                    (u64*)nullptr, (float*)nullptr, (u32*)nullptr, derr);
         // the place reserved for a query: all its hits, or at most maxPoints per block of its index box

@@ -629,6 +629,167 @@ __global__ void __launch_bounds__(TRB_THREADS)
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Small maxPoints (1 .. 32, and at most TRK_CAP candidates per query = blocks of the index box x maxPoints): no hit list.
+// Each block of the box is searched for its maxPoints nearest points with d2 < r2 - exactly what the per-block cut keeps -
+// by the bounded branch and bound of the k-NN search (cells farther than the k-th best so far are never opened), one
+// warp per query, lane i holding the i-th best of the block. The candidates of all blocks (<= TRK_CAP) are then ordered
+// in the warp's shared memory by counting smaller keys (keys {d2 : rank} are unique), the last of every run of equal d2
+// survives (std::map semantics), and the survivors are written in order at the query's fixed-stride place; the caller
+// packs them. Same results as the hit-list path: at r = 2 m on the C4 map a query has 5000 hits and keeps < 32.
+constexpr u32 TRK_CAP = 256, TRK_WARPS = 4;
+struct TopKVisitor
+{
+    float q[3], r2;
+    float ld, lx, ly, lz, wb;
+    u32   li, k;
+    __device__ __forceinline__ void init(float x, float y, float z, u32 k_, float r2_)
+    {
+        q[0] = x, q[1] = y, q[2] = z, k = k_, r2 = r2_;
+        reset();
+    }
+    __device__ __forceinline__ void reset()
+    {
+        ld = __int_as_float(0x7f800000);
+        wb = r2;
+        li = 0xFFFFFFFFu;
+        lx = ly = lz = 0.f;
+    }
+    __device__ __forceinline__ float bound() const { return wb; }
+    __device__ __forceinline__ void  row(const float4& p, bool valid)
+    {
+        const int   lane = lane_id();
+        const float d    = valid ? sqr_dist(q[0], q[1], q[2], p.x, p.y, p.z) : 0.f;
+        const u32   i    = __float_as_uint(p.w);
+        const float kd   = __shfl_sync(MMG_FULL, ld, k - 1);
+        const u32   ki   = __shfl_sync(MMG_FULL, li, k - 1);
+        u32         m    = __ballot_sync(MMG_FULL, valid && d < r2 && (d < kd || (d == kd && i < ki)));
+        while (m)
+        {
+            const int j = __ffs(m) - 1;
+            m &= m - 1;
+            const float cd = __shfl_sync(MMG_FULL, d, j), cx = __shfl_sync(MMG_FULL, p.x, j), cy = __shfl_sync(MMG_FULL, p.y, j),
+                        cz = __shfl_sync(MMG_FULL, p.z, j);
+            const u32 ci  = __shfl_sync(MMG_FULL, i, j);
+            const u32 pos = __popc(__ballot_sync(MMG_FULL, ld < cd || (ld == cd && li < ci)));
+            if (pos >= k) continue;
+            const float ud = __shfl_up_sync(MMG_FULL, ld, 1), ux = __shfl_up_sync(MMG_FULL, lx, 1), uy = __shfl_up_sync(MMG_FULL, ly, 1),
+                        uz = __shfl_up_sync(MMG_FULL, lz, 1);
+            const u32 ui   = __shfl_up_sync(MMG_FULL, li, 1);
+            if ((u32)lane > pos) ld = ud, li = ui, lx = ux, ly = uy, lz = uz;
+            if ((u32)lane == pos) ld = cd, li = ci, lx = cx, ly = cy, lz = cz;
+        }
+    }
+    // a full list bounds the search by its k-th distance (ties at that distance with a lower index still enter: the cell
+    // test is "lower bound > bound"), an incomplete one by the radius
+    __device__ __forceinline__ void cell_done()
+    {
+        const float kd = __shfl_sync(MMG_FULL, ld, k - 1);
+        wb             = fminf(r2, kd);
+    }
+};
+
+__global__ void __launch_bounds__(TRK_WARPS * 32)
+    k_trees_radius_topk(TreesDev t, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 n, PoseD pose, int use_pose,
+                        float r2, float r, u32 maxp, u32 stride /*places per query*/, float* __restrict__ rxyz, float* __restrict__ rd2, u64* __restrict__ rid,
+                        u32* __restrict__ outcnt, TreesRadiusErr* __restrict__ err)
+{
+    __shared__ u64   s_key[TRK_WARPS][TRK_CAP];
+    __shared__ float s_xyz[TRK_WARPS][TRK_CAP * 3];
+    __shared__ u32   s_idx[TRK_WARPS][TRK_CAP];
+    const int lane = lane_id(), wid = threadIdx.x >> 5;
+    u64*      key = s_key[wid];
+    float*    xyz = s_xyz[wid];
+    u32*      idx = s_idx[wid];
+    const u32 nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (u32 q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < n; q += nwarps)
+    {
+        float3 p = make_float3(qx[q], qy[q], qz[q]);
+        if (use_pose) p = compose_point(pose, p.x, p.y, p.z);
+        int        a[3], b[3];
+        const bool ok = trees_radius_box(t, p, r, a, b);
+        u32        N = 0, rank0 = 0;
+        if (ok && r2 > 0.f)
+        {
+            TopKVisitor v;
+            v.init(p.x, p.y, p.z, maxp, r2);
+            for (int x = a[0]; x <= b[0]; x++)
+                for (int y = a[1]; y <= b[1]; y++)
+                    for (int z = a[2]; z <= b[2]; z++)
+                    {
+                        u32 bid, ecnt;
+                        if (!index_in_range(x, y, z) || !probe_ro(t.btab, t.bmask, pack_key(x, y, z), bid, ecnt)) continue;
+                        const BlockGeom g = trees_geom(t, x, y, z);
+                        v.reset();
+                        trees_traverse(t, bid, g, v.q, v);
+                        const bool mine = (u32)lane < maxp && v.li != 0xFFFFFFFFu;
+                        const u32  c    = __popc(__ballot_sync(MMG_FULL, mine));
+                        if (mine && N + (u32)lane < TRK_CAP)
+                        {
+                            const u32 o = N + (u32)lane;
+                            key[o]      = ((u64)__float_as_uint(v.ld) << 32) | (u64)(rank0 + v.li);
+                            xyz[3 * o] = v.lx, xyz[3 * o + 1] = v.ly, xyz[3 * o + 2] = v.lz;
+                            idx[o] = v.li;
+                        }
+                        N += c;
+                        const u32 bc = __ldg(&t.bcnt[bid]);
+                        if (rank0 + bc < rank0 && lane == 0) atomicAdd(&err->rank_overflow, 1u);
+                        rank0 += bc;
+                    }
+        }
+        N = min(N, TRK_CAP);  // (the host sizes stride = blocks x maxPoints <= TRK_CAP: never cut)
+        __syncwarp();
+        // survivors: no other candidate with the same d2 and a higher rank; place = survivors with a smaller key
+        u32 mykeep = 0;  // bit e: candidate lane + 32 e survives
+        for (u32 e = 0; e * 32 < N; e++)
+        {
+            const u32 i = e * 32 + lane;
+            if (i >= N) continue;
+            const u64 ki  = key[i];
+            bool      dup = false;
+            for (u32 j = 0; j < N; j++)
+            {
+                const u64 kj = key[j];
+                dup |= (u32)(kj >> 32) == (u32)(ki >> 32) && kj > ki;
+            }
+            if (!dup) mykeep |= 1u << e;
+        }
+        __syncwarp();
+        // mark the dropped ones (top bit set: sorts after everything, never counted as "smaller" for a survivor's place)
+        for (u32 e = 0; e * 32 < N; e++)
+        {
+            const u32 i = e * 32 + lane;
+            if (i < N && !((mykeep >> e) & 1u)) key[i] |= 1ull << 63;
+        }
+        __syncwarp();
+        u32       kept = 0;
+        const u64 ob   = (u64)q * stride;
+        for (u32 e = 0; e * 32 < N; e++)
+        {
+            const u32  i    = e * 32 + lane;
+            const bool keep = i < N && ((mykeep >> e) & 1u);
+            if (keep)
+            {
+                const u64 ki  = key[i];
+                u32       pos = 0;
+                for (u32 j = 0; j < N; j++) pos += key[j] < ki;
+                const u64 o = ob + pos;
+                rxyz[3 * o] = xyz[3 * i], rxyz[3 * o + 1] = xyz[3 * i + 1], rxyz[3 * o + 2] = xyz[3 * i + 2];
+                rd2[o] = __uint_as_float((u32)(ki >> 32));
+                rid[o] = (u64)idx[i];
+            }
+            kept += __popc(__ballot_sync(MMG_FULL, keep));
+        }
+        if (lane == 0) outcnt[q] = kept;
+        __syncwarp();
+    }
+}
+static __global__ void k_trees_radius_stride_offsets(u32 n, u32 stride, u64* __restrict__ boff)
+{
+    const u32 q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q <= n) boff[q] = (u64)q * stride;
+}
+
 // moves the survivors of every query from its reserved place (boff) to its final place (noff); one warp per query
 static __global__ void k_trees_radius_pack(u32 n, const u32* __restrict__ outcnt, const u64* __restrict__ boff, const u64* __restrict__ noff,
                                            const float* __restrict__ sxyz, const float* __restrict__ sd2, const u64* __restrict__ sid,

@@ -275,8 +275,19 @@ def test_sparse_trees_radius_duplicates_ties_and_chunks(built):
         # r = 6 m: every query sees tens of thousands of raw hits (> 16384: global-memory sort) that collapse to <= 700
         raw = g.nn_radius(*q, np.float32(36.0), 0)
         assert int(np.diff(raw[0]).max()) <= 700
+        # small maxPoints take the per-block bounded k-nearest path (k_trees_radius_topk): same answers as the reference and
+        # as the hit-list path, with 60-fold duplicates at every distance and mirror ties across the block boundary
+        # (r = 2 m: 8 blocks per query, 8 x 32 = 256 candidates = the path's limit; r = 6 m, maxPoints 9: 27 x 9 = 243)
+        for r, mp in ((2.0, 1), (2.0, 7), (2.0, 32), (3.5, 16), (6.0, 9)):
+            capi.check(lib.mmg_set_tuning(b"radius_topk", 1))
+            assert _same_radius(g, o, q, r, mp) > 0
+            a = g.nn_radius(*q, np.float32(r * r), mp)
+            capi.check(lib.mmg_set_tuning(b"radius_topk", 0))
+            b = g.nn_radius(*q, np.float32(r * r), mp)
+            assert all(np.array_equal(np.asarray(x).view(np.uint8), np.asarray(y).view(np.uint8)) for x, y in zip(a, b))
     finally:
         capi.check(lib.mmg_set_tuning(b"radius_chunk_hits", 1 << 26))
+        capi.check(lib.mmg_set_tuning(b"radius_topk", 1))
 
 
 def test_sparse_voxel_radius_split_batches(built):
