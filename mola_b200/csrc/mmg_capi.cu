@@ -20,7 +20,7 @@
 namespace mmg
 {
 std::atomic<unsigned long long> g_launches{0};
-int                       g_tune[T_COUNT] = {0, 16, 4096, 1, 1 << 26, 0x7FFFFFFF, 6, 2048, 6144, 1, 1};
+int                       g_tune[T_COUNT] = {0, 16, 4096, 1, 1 << 26, 0x7FFFFFFF, 6, 1024, 6144, 2, 1};
 static thread_local char  g_err[512] = "";
 void set_error(const char* fmt, ...)
 {

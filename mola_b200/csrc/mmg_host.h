@@ -159,7 +159,8 @@ enum Tune
     T_NN_TASK_MINB,       // k_nn_tasks: resident blocks of 256 per SM it is compiled for (5 | 6 | 8)
     T_RADIUS_WARP_MAX,    // SparseTrees radius search: lists up to this many hits are sorted by a warp, longer ones by a block
     T_RADIUS_BLOCK_MID,   // SparseTrees radius search: lists up to this many hits share an SM three blocks at a time
-    T_RADIUS_Q16,         // SparseTrees radius search: sort on the 16-bit monotone image of d2 (1) or on the raw key bits (0)
+    T_RADIUS_Q16,         // SparseTrees radius search: 2 = one bucket pass on the monotone 16-bit image of d2 + per-bucket insertion sort,
+                          // 1 = two radix passes on that image + run fix, 0 = radix on the raw key bits
     T_RADIUS_TOPK,        // SparseTrees radius search with maxPoints <= 32: per-block bounded k-nearest search (1) or the hit-list path (0)
     T_COUNT
 };

@@ -666,7 +666,7 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
                 MMG_LAUNCH(k_trees_radius_sort, (unsigned)std::min<size_t>((k + TRR_WARPS - 1) / TRR_WARPS, sblocks), TRR_THREADS, 0, st, s->dev, dx, dy, dz,
                            (u32)a, (u32)k, T, pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey,
                            (const float*)hxyz, (const u32*)hidx, bufk, bufp, hmax, gtab, nbq32, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next, n_small,
-                           n_large, qscale);
+                           n_large, qscale, g_tune[T_RADIUS_Q16] >= 2 ? 1 : 0);
                 if (n_large > n_small)
                 {
                     static bool attr_set = false;
@@ -686,7 +686,7 @@ int trees_radius(mmg_map* m, const float* xs, const float* ys, const float* zs, 
                         const unsigned bpsm = (unsigned)std::max<size_t>(1, std::min<size_t>(4, (220 * 1024) / (smem + 26 * 1024)));
                         MMG_LAUNCH(k_trees_radius_sort_block, (unsigned)std::min<size_t>(k, (size_t)m->num_sms * bpsm), TRB_THREADS, smem, st, s->dev, dx, dy,
                                    dz, (u32)a, (u32)k, T, pose12 ? 1 : 0, r, maxp, (const u32*)(cnt + a), (const u64*)off, hoff[a], (const u64*)hkey,
-                                   (const float*)hxyz, (const u32*)hidx, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next + 1 + c, lo[c], hi[c], qscale);
+                                   (const float*)hxyz, (const u32*)hidx, (const u64*)boff, rxyz, rd2, rid, outcnt + a, next + 1 + c, lo[c], hi[c], qscale, g_tune[T_RADIUS_Q16] >= 2 ? 1 : 0);
                     }
                 }
             }

@@ -181,6 +181,72 @@ __device__ __forceinline__ void warp_radix_pass(const u64* __restrict__ sk, cons
         __syncwarp();
     }
 }
+// One-pass alternative to the two quantised radix passes: the hits are dropped into TRR_BINS buckets by the top bits of
+// q16 (buckets are in distance order because q16 is monotone; the order inside a bucket does not matter), and every bucket
+// - one to three hits on average - is then put in exact 64-bit key order by an insertion sort. One counting pass and one
+// scatter with shared-memory atomics, no stable ranking. Returns false (nothing usable in A) when a bucket holds more than
+// 64 hits (thousands of duplicated points): the caller then sorts on the raw key bits.
+constexpr u32 TRR_BINS = 1024;
+__device__ __forceinline__ bool warp_bucket_sort(const u64* __restrict__ key, HitBuf A, u32 N, float qscale, u32* hist /*TRR_BINS*/)
+{
+    const int lane = lane_id();
+    constexpr u32 PER = TRR_BINS / 32;
+#pragma unroll
+    for (u32 e = 0; e < PER; e++) hist[lane * PER + e] = 0;
+    __syncwarp();
+    for (u32 i = lane; i < N; i += 32) atomicAdd(&hist[trr_q16(key[i], qscale) >> 6], 1u);
+    __syncwarp();
+    bool big = false;
+    {
+        u32 sum = 0;
+#pragma unroll
+        for (u32 e = 0; e < PER; e++)
+        {
+            const u32 v = hist[lane * PER + e];
+            big |= v > 64u;
+            sum += v;
+        }
+        u32 incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const u32 y = __shfl_up_sync(MMG_FULL, incl, o);
+            if (lane >= o) incl += y;
+        }
+        u32 base = incl - sum;
+#pragma unroll
+        for (u32 e = 0; e < PER; e++)
+        {
+            const u32 v          = hist[lane * PER + e];
+            hist[lane * PER + e] = base;
+            base += v;
+        }
+    }
+    __syncwarp();
+    if (__any_sync(MMG_FULL, big)) return false;
+    for (u32 i = lane; i < N; i += 32)
+    {
+        const u64 k  = key[i];
+        const u32 at = atomicAdd(&hist[trr_q16(k, qscale) >> 6], 1u);
+        A.k[at] = k, A.p[at] = i;
+    }
+    __syncwarp();
+    // hist[b] is now the END of bucket b
+    for (u32 b = lane; b < TRR_BINS; b += 32)
+    {
+        const u32 beg = b ? hist[b - 1] : 0u, end = hist[b];
+        for (u32 a = beg + 1; a < end; a++)
+        {
+            const u64 ka = A.k[a];
+            const u32 pa = A.p[a];
+            u32       c  = a;
+            for (; c > beg && A.k[c - 1] > ka; c--) A.k[c] = A.k[c - 1], A.p[c] = A.p[c - 1];
+            A.k[c] = ka, A.p[c] = pa;
+        }
+    }
+    __syncwarp();
+    return true;
+}
 // sorts the N pairs (key[i], i) by key; returns the buffer that holds the result
 __device__ __forceinline__ HitBuf warp_radix_sort(const u64* __restrict__ key, HitBuf A, HitBuf B, u32 N, float qscale, u32* hist)
 {
@@ -257,12 +323,13 @@ __global__ void __launch_bounds__(TRR_THREADS)
                         const u64* __restrict__ key, const float* __restrict__ hxyz, const u32* __restrict__ hidx, u64* __restrict__ bufk,
                         u32* __restrict__ bufp, u64 hc /*hits of the chunk: bufk / bufp hold two buffers of that length*/, u32* __restrict__ gtab,
                         u32 nbq /*gtab: 2 * nbq words per warp of the grid*/, const u64* __restrict__ boff, float* __restrict__ rxyz,
-                        float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt, u32* __restrict__ next_query, u32 n_small, u32 n_large, float qscale)
+                        float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt, u32* __restrict__ next_query, u32 n_small, u32 n_large, float qscale,
+                        int bucket)
 {
     // this kernel takes the queries with at most n_small hits (their lists stay in L2 however many warps run) and those with
     // more than n_large (too long for the block kernel's shared memory); k_trees_radius_sort_block takes the ones in between
     constexpr u32  ACC = 1u << 31, SURV = 1u << 30, IDX = SURV - 1u;
-    __shared__ u32 s_hist[TRR_WARPS][256];
+    __shared__ u32 s_hist[TRR_WARPS][TRR_BINS];
     const int      lane = lane_id(), wid = threadIdx.x >> 5;
     u32*           hist  = s_hist[wid];
     u32*           rank0 = gtab + (size_t)(blockIdx.x * TRR_WARPS + wid) * 2 * nbq;
@@ -282,7 +349,9 @@ __global__ void __launch_bounds__(TRR_THREADS)
         if (N > n_small && N <= n_large) continue;
         const u64    h0 = off[q] - off_base;
         const HitBuf A{bufk + h0, bufp + h0}, B{bufk + hc + h0, bufp + hc + h0};
-        HitBuf       S = warp_radix_sort(key + h0, A, B, N, qscale, hist);
+        HitBuf       S = A;
+        // (lists of a few dozen hits: clearing and scanning the buckets costs more than the second radix pass saves)
+        if (!(bucket && qscale > 0.f && N >= 192u && warp_bucket_sort(key + h0, A, N, qscale, hist))) S = warp_radix_sort(key + h0, A, B, N, qscale, hist);
         __syncwarp();
         if (maxp == 0)
         {   // every hit enters the map: the last of each run of equal d2 survives
@@ -466,12 +535,65 @@ __device__ __forceinline__ unsigned short* block_radix_perm(const u64* __restric
     return posA;
 }
 
+// The block kernel's form of warp_bucket_sort: 4096 buckets (the top 12 bits of q16) in the shared histogram, the permutation
+// scattered with shared-memory atomics, every bucket (one to four hits on average) insertion-sorted on the full key by one
+// thread. Returns false when a bucket is too long.
+__device__ __forceinline__ bool block_bucket_perm(const u64* __restrict__ key, unsigned short* pos, u32 N, u32* hist /*4096*/, u32* s_scan /*TRB_WARPS*/,
+                                                  u32* s_flag, float qscale)
+{
+    constexpr int NB = 256 * TRB_WARPS, E = NB / TRB_THREADS;
+    const int     lane = lane_id(), w = threadIdx.x >> 5;
+    for (u32 i = threadIdx.x; i < (u32)NB; i += blockDim.x) hist[i] = 0;
+    if (threadIdx.x == 0) *s_flag = 0;
+    __syncthreads();
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) atomicAdd(&hist[trr_q16(key[i], qscale) >> 4], 1u);
+    __syncthreads();
+    {
+        u32  v[E], sum = 0;
+        bool big = false;
+#pragma unroll
+        for (int e = 0; e < E; e++) v[e] = hist[threadIdx.x * E + e], sum += v[e], big |= v[e] > 64u;
+        if (big) *s_flag = 1;
+        u32 incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const u32 y = __shfl_up_sync(MMG_FULL, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) s_scan[w] = incl;
+        __syncthreads();
+        u32 base = incl - sum;
+        for (int k = 0; k < w; k++) base += s_scan[k];
+#pragma unroll
+        for (int e = 0; e < E; e++) hist[threadIdx.x * E + e] = base, base += v[e];
+    }
+    __syncthreads();
+    if (*s_flag) return false;
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) pos[atomicAdd(&hist[trr_q16(key[i], qscale) >> 4], 1u)] = (unsigned short)i;
+    __syncthreads();
+    for (u32 b = threadIdx.x; b < (u32)NB; b += blockDim.x)
+    {
+        const u32 beg = b ? hist[b - 1] : 0u, end = hist[b];  // hist[b] is now the END of bucket b
+        for (u32 a = beg + 1; a < end; a++)
+        {
+            const unsigned short pa = pos[a];
+            const u64            ka = key[pa];
+            u32                  c  = a;
+            for (; c > beg && key[pos[c - 1]] > ka; c--) pos[c] = pos[c - 1];
+            pos[c] = pa;
+        }
+    }
+    __syncthreads();
+    return true;
+}
+
 __global__ void __launch_bounds__(TRB_THREADS)
     k_trees_radius_sort_block(TreesDev t, const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qz, u32 q0, u32 n,
                               PoseD pose, int use_pose, float r, u32 maxp, const u32* __restrict__ cnt, const u64* __restrict__ off, u64 off_base,
                               const u64* __restrict__ key, const float* __restrict__ hxyz, const u32* __restrict__ hidx, const u64* __restrict__ boff,
                               float* __restrict__ rxyz, float* __restrict__ rd2, u64* __restrict__ rid, u32* __restrict__ outcnt,
-                              u32* __restrict__ next_query, u32 n_small, u32 n_large, float qscale)
+                              u32* __restrict__ next_query, u32 n_small, u32 n_large, float qscale, int bucket)
 {
     constexpr unsigned short ACC = 1u << 15, SURV = 1u << 14, IDX = SURV - 1u;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -512,32 +634,40 @@ __global__ void __launch_bounds__(TRB_THREADS)
         }
         for (u32 i = threadIdx.x; i < N; i += blockDim.x) skey[i] = key[h0 + i];
         __syncthreads();
-        unsigned short* sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, qscale);
-        if (qscale > 0.f)
-        {   // exact (d2, rank) order inside the runs of equal q16: the thread that meets a run's head sorts the run
-            if (threadIdx.x == 0) s_flag = 0;
-            __syncthreads();
-            for (u32 i = threadIdx.x; i < N; i += blockDim.x)
-            {
-                const u32 qi = trr_q16(skey[sp[i]], qscale);
-                if ((i == 0 || trr_q16(skey[sp[i - 1]], qscale) != qi) && i + 1 < N && trr_q16(skey[sp[i + 1]], qscale) == qi)
+        unsigned short* sp = spos;
+        if (bucket && qscale > 0.f)
+        {
+            if (!block_bucket_perm(skey, spos, N, s_hist, s_scan, &s_flag, qscale)) sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, 0.f);
+        }
+        else
+        {
+            sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, qscale);
+            if (qscale > 0.f)
+            {   // exact (d2, rank) order inside the runs of equal q16: the thread that meets a run's head sorts the run
+                if (threadIdx.x == 0) s_flag = 0;
+                __syncthreads();
+                for (u32 i = threadIdx.x; i < N; i += blockDim.x)
                 {
-                    u32 e = i + 2;
-                    while (e < N && trr_q16(skey[sp[e]], qscale) == qi) e++;
-                    if (e - i > 64) s_flag = 1;
-                    else
-                        for (u32 a = i + 1; a < e; a++)
-                        {
-                            const unsigned short pa = sp[a];
-                            const u64            ka = skey[pa];
-                            u32                  b  = a;
-                            for (; b > i && skey[sp[b - 1]] > ka; b--) sp[b] = sp[b - 1];
-                            sp[b] = pa;
-                        }
+                    const u32 qi = trr_q16(skey[sp[i]], qscale);
+                    if ((i == 0 || trr_q16(skey[sp[i - 1]], qscale) != qi) && i + 1 < N && trr_q16(skey[sp[i + 1]], qscale) == qi)
+                    {
+                        u32 e = i + 2;
+                        while (e < N && trr_q16(skey[sp[e]], qscale) == qi) e++;
+                        if (e - i > 64) s_flag = 1;
+                        else
+                            for (u32 a = i + 1; a < e; a++)
+                            {
+                                const unsigned short pa = sp[a];
+                                const u64            ka = skey[pa];
+                                u32                  b  = a;
+                                for (; b > i && skey[sp[b - 1]] > ka; b--) sp[b] = sp[b - 1];
+                                sp[b] = pa;
+                            }
+                    }
                 }
+                __syncthreads();
+                if (s_flag) sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, 0.f);
             }
-            __syncthreads();
-            if (s_flag) sp = block_radix_perm(skey, spos, spos2, N, s_hist, s_red, s_scan, 0.f);
         }
         auto K = [&](u32 i) -> u64 { return skey[sp[i] & IDX]; };
         if (maxp == 0)
